@@ -1,0 +1,27 @@
+# Builds libg16b200.so (CUDA, sm_100a) and the `prover` CLI in-tree.  nvcc cross-compiles without a GPU.
+PKG      := zk-proof-of-assets_b200
+CSRC     := $(PKG)/csrc
+NVCC     ?= nvcc
+ARCH     := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
+OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o
+HDRS     := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.hpp) include/g16_b200.h
+
+all: $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover
+
+$(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(PKG)/libg16b200.so: $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+
+$(PKG)/libg16synth.so: $(CSRC)/synth.o
+	$(NVCC) $(ARCH) -shared -o $@ $< -lcudart
+
+$(PKG)/prover: $(CSRC)/prover_main.cpp include/g16_b200.h $(PKG)/libg16b200.so
+	g++ -O2 -std=c++17 -Iinclude $< -o $@ -L$(PKG) -lg16b200 -Wl,-rpath,'$$ORIGIN'
+
+clean:
+	rm -f $(CSRC)/*.o $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover
+
+.PHONY: all clean

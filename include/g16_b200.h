@@ -1,0 +1,128 @@
+/*
+ * g16_b200.h -- C ABI of the B200-native Groth16/BN254 prover (libg16b200.so).
+ *
+ * Drop-in boundary for the `groth16 prove` step of silversixpence-crypto/zk-proof-of-assets:
+ *   scripts/g16_prove.sh:246-252   "$rapidsnark_path" <zkey> <wtns> <proof.json> <public.json>
+ *   scripts/g16_prove.sh:253-259   npx snarkjs groth16 prove <zkey> <wtns> <proof.json> <public.json>
+ *   git_modules/circom-ecdsa/scripts/groupsign_cli.ts:114   snarkjs.groth16.prove(zkeyFileName, wtnsFileName)
+ * The reference holds no prover source; the upstream homes of each replaced function are
+ * cited per entry point.  Plain pointers and sizes only; every function returns a g16_status.
+ *
+ * Threading: distinct g16_zkey handles may be used from distinct threads; one prove in flight per handle.
+ * All byte strings are little-endian; field elements are 32 bytes; "standard form" = not Montgomery.
+ */
+#ifndef G16_B200_H
+#define G16_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    G16_OK = 0,
+    G16_ERR_GENERIC = 1,       /* message in g16_last_error() */
+    G16_ERR_SHORT_BUFFER = 2,  /* required sizes written back to *proof_len / *public_len */
+    G16_ERR_WITNESS_LEN = 3,   /* "Invalid witness length. Circuit: N, witness: M" (snarkjs groth16_prove.js) */
+    G16_ERR_CURVE = 4,         /* "Curve of the witness does not match the curve of the proving key" */
+    G16_ERR_CUDA = 5,          /* no device / CUDA failure: there is no CPU fallback */
+    G16_ERR_FORMAT = 6         /* malformed .zkey / .wtns container */
+} g16_status;
+
+enum { G16_STYLE_RAPIDSNARK = 0, G16_STYLE_SNARKJS = 1 };
+
+typedef struct g16_zkey g16_zkey; /* proving key parsed once and kept resident on one GPU */
+
+typedef struct {
+    int32_t device;      /* CUDA ordinal; -1 = current device */
+    int32_t style;       /* output byte layout: G16_STYLE_RAPIDSNARK (what full_workflow.sh produces) or _SNARKJS */
+    int32_t has_rs;      /* 1 = use r,s below (TEST HOOK; neither upstream prover can pin them) */
+    uint8_t r[32];       /* blinding factors, standard form */
+    uint8_t s[32];
+    int32_t msm_c;       /* Pippenger window bits, 0 = automatic */
+    int32_t shard_rank;  /* base-range sharding of every MSM across GPUs: this handle holds slice rank/count */
+    int32_t shard_count; /* 0 or 1 = whole key */
+    int32_t reserved[8];
+} g16_opts;
+
+void g16_opts_default(g16_opts* o);
+const char* g16_last_error(void); /* thread-local, valid until the next call on this thread */
+const char* g16_version(void);
+
+/* ---- proving key: replaces snarkjs zkey_utils.js readHeader + section reads / rapidsnark ZKeyUtils::loadHeader
+ *      (rows a1, a2).  Uploads sections 4-9 to the GPU (only the shard's slice of 5-9). */
+int g16_zkey_open(const char* path, const g16_opts* opts, g16_zkey** out);
+int g16_zkey_open_mem(const uint8_t* data, size_t len, const g16_opts* opts, g16_zkey** out);
+void g16_zkey_close(g16_zkey* zk);
+int g16_zkey_info(const g16_zkey* zk, uint32_t* n_vars, uint32_t* n_public, uint32_t* domain_size, uint64_t* n_coefs);
+
+/* ---- prove: replaces snarkjs groth16_prove.js groth16Prove / rapidsnark Groth16::Prover::prove (rows a3-a16).
+ * wtns = the bytes of a .wtns file.  On success the JSON texts (no trailing NUL counted) are in the caller's
+ * buffers and their lengths in *proof_len / *public_len (in: capacity, out: length). */
+int g16_prove(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len, char* proof_json, size_t* proof_len,
+              char* public_json, size_t* public_len, const g16_opts* opts);
+
+/* same, split so that a caller can keep the witness resident: load = parse + host->device copy */
+int g16_witness_load(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len);
+int g16_prove_loaded(g16_zkey* zk, char* proof_json, size_t* proof_len, char* public_json, size_t* public_len,
+                     const g16_opts* opts);
+
+/* the rapidsnark / snarkjs command line as one call: reads both files, writes both outputs */
+int g16_prove_files(const char* zkey_path, const char* wtns_path, const char* proof_path, const char* public_path,
+                    const g16_opts* opts);
+
+/* ---- multi-GPU: every rank holds a base-range shard (opts.shard_rank/shard_count at open), computes its partial
+ * sums of the five MSMs, and one rank combines.  A partial is G16_PARTIAL_BYTES: XYZZ Montgomery points
+ * A, B1, C, H (4 x 128 B) then B2 (256 B).  The exchange (NCCL all_gather of 768 B) belongs to the caller. */
+#define G16_PARTIAL_BYTES 768
+int g16_prove_partial(g16_zkey* zk, uint8_t* partial_out);
+int g16_prove_combine(g16_zkey* zk, const uint8_t* partials, int count, char* proof_json, size_t* proof_len,
+                      char* public_json, size_t* public_len, const g16_opts* opts);
+
+/* ---- operators on the path, usable on their own (metric: BN254 MSM Mpts/s; NTT GB/s) ------------------------
+ * MSM: bases = zkey records (affine, Montgomery, all-zero = infinity; 64 B G1 / 128 B G2), scalars = 32 B standard
+ * form.  *_host take host pointers (copies inside), *_dev take device pointers.  Result: affine, Montgomery,
+ * zkey record layout (all-zero = infinity).  Replaces ffjavascript engine_multiexp.js multiExpAffine (rows a9-a13). */
+int g16_msm_g1_host(const uint8_t* bases, const uint8_t* scalars, size_t n, uint8_t out[64], const g16_opts* opts);
+int g16_msm_g2_host(const uint8_t* bases, const uint8_t* scalars, size_t n, uint8_t out[128], const g16_opts* opts);
+
+typedef struct g16_msm g16_msm; /* reusable workspace for device-resident MSMs */
+int g16_msm_create(int is_g2, size_t max_n, const g16_opts* opts, g16_msm** out);
+void g16_msm_destroy(g16_msm* m);
+int g16_msm_run_dev(g16_msm* m, const void* d_bases, const void* d_scalars, size_t n, uint8_t* out_affine);
+/* counters of the last run: [0] non-zero digits (= mixed additions), [1] tasks, [2] cut buckets, [3] buckets,
+ * [4] window bits, [5] windows */
+int g16_msm_stats(const g16_msm* m, uint64_t out[6]);
+
+/* H-polynomial pipeline on its own (rows a4-a8): witness already loaded; out = domain_size x 32 B standard form
+ * (the scalars of the H MSM), host buffer. */
+int g16_h_scalars(g16_zkey* zk, uint8_t* out);
+/* odd-coset transform of `count` device-resident vectors of 2^logn Montgomery Fr elements, in place:
+ * iNTT, multiply by inc^i, NTT (rows a5-a7).  d_data: count x 2^logn x 32 B. */
+int g16_coset_ntt_dev(void* d_data, int logn, int count);
+int g16_coset_ntt_host(uint8_t* data, int logn);
+
+/* ---- field / curve micro-operators (parity tests against the oracle; n elements, host buffers) ------------- */
+int g16_test_field_op(int field /*0 Fq, 1 Fr*/, int op /*0 mul, 1 add, 2 sub, 3 to_mont, 4 from_mont, 5 inv*/,
+                      const uint8_t* a, const uint8_t* b, uint8_t* out, size_t n);
+/* op 0: XYZZ acc (identity) += each affine point in turn via mixed add, over n points -> affine sum
+ * op 1: tree of full XYZZ additions -> affine sum;  op 2: 2*P per point (out n affine points) */
+int g16_test_curve_op(int is_g2, int op, const uint8_t* points, size_t n, uint8_t* out);
+
+/* ---- measurement helpers ---------------------------------------------------------------------------------- */
+/* per-phase device times of the last prove on this handle, milliseconds (CUDA events):
+ * [0] h2d witness [1] r1cs eval [2] ntt pipeline [3] msm A [4] msm B1 [5] msm B2 [6] msm C [7] msm H
+ * [8] whole device region [9] host finalisation */
+int g16_last_timings(const g16_zkey* zk, double out_ms[10]);
+/* counters of the last prove: per MSM (A,B1,B2,C,H) x {mixed additions, tasks, cut buckets, c, W} */
+int g16_last_msm_stats(const g16_zkey* zk, uint64_t out[25]);
+/* integer-pipe microbenchmark: op 0 = 32-bit IMAD, 1 = IMAD.WIDE.U32 (+carry chain), 2 = Montgomery products.
+ * Returns achieved ops per second over the whole device (op 2: field products per second). */
+int g16_bench_int_pipe(int op, double* ops_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,377 @@
+// BN254 prime fields on the sm_100a integer pipe: 8 x 32-bit limbs, Montgomery form (R = 2^256).
+//
+// Replaces: wasmcurves 0.2.2 build_f1m / rapidsnark fr.asm+fq.asm (4x64 Montgomery).
+// Call sites in the reference: scripts/g16_prove.sh:246-260.  Byte layout of an element is the
+// zkey/wtns one: 32 bytes little-endian, so device buffers are the file bytes.
+//
+// mul(): operand-scanning Montgomery product with the reduction interleaved.  Partial products of the
+// even limbs of `a` and of the odd limbs of `a` are kept in two accumulators one limb apart, so every
+// 32x32->64 product lands on an aligned register pair and a row is four carry chains of
+// mad.lo.cc/madc.hi.cc (ptxas pairs them into IMAD.WIDE.U32 + carry).  128 wide MADs + 8 single
+// MULs per product = the 136-op work model of SURVEY.md section 8(d).  The design was checked limb for
+// limb by scratch/montsim.py before it was written here.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace g16 {
+
+struct alignas(16) fe_t {
+    uint32_t v[8];
+};
+
+struct FqParams {
+    static __host__ __device__ __forceinline__ constexpr uint32_t mod(int i) {
+        const uint32_t t[8] = {0xd87cfd47u, 0x3c208c16u, 0x6871ca8du, 0x97816a91u, 0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return t[i];
+    }
+    static __host__ __device__ __forceinline__ constexpr uint32_t r1(int i) {
+        const uint32_t t[8] = {0xc58f0d9du, 0xd35d438du, 0xf5c70b3du, 0x0a78eb28u, 0x7879462cu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return t[i];
+    }
+    static __host__ __device__ __forceinline__ constexpr uint32_t r2(int i) {
+        const uint32_t t[8] = {0x538afa89u, 0xf32cfc5bu, 0xd44501fbu, 0xb5e71911u, 0x0a417ff6u, 0x47ab1effu, 0xcab8351fu, 0x06d89f71u};
+        return t[i];
+    }
+    static constexpr uint32_t INV = 0xe4866389u;  // -MOD^-1 mod 2^32
+};
+
+struct FrParams {
+    static __host__ __device__ __forceinline__ constexpr uint32_t mod(int i) {
+        const uint32_t t[8] = {0xf0000001u, 0x43e1f593u, 0x79b97091u, 0x2833e848u, 0x8181585du, 0xb85045b6u, 0xe131a029u, 0x30644e72u};
+        return t[i];
+    }
+    static __host__ __device__ __forceinline__ constexpr uint32_t r1(int i) {
+        const uint32_t t[8] = {0x4ffffffbu, 0xac96341cu, 0x9f60cd29u, 0x36fc7695u, 0x7879462eu, 0x666ea36fu, 0x9a07df2fu, 0x0e0a77c1u};
+        return t[i];
+    }
+    static __host__ __device__ __forceinline__ constexpr uint32_t r2(int i) {
+        const uint32_t t[8] = {0xae216da7u, 0x1bb8e645u, 0xe35c59e3u, 0x53fe3ab1u, 0x53bb8085u, 0x8c49833du, 0x7f4e44a5u, 0x0216d0b1u};
+        return t[i];
+    }
+    static constexpr uint32_t INV = 0xefffffffu;
+};
+
+// ---- carry-chain building blocks (one asm statement per chain: the carry flag never crosses statements)
+
+// acc[0..7] += {x0,x1,x2,x3} * y, product k on limbs (2k, 2k+1); returns the carry out of limb 7
+__device__ __forceinline__ uint32_t mad_row_c(uint32_t (&acc)[8], uint32_t x0, uint32_t x1, uint32_t x2,
+                                              uint32_t x3, uint32_t y) {
+    uint32_t c;
+    asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\t"
+        "madc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %2;\n\t"
+        "madc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %4;\n\t"
+        "madc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, %6;\n\t"
+        "madc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+        "addc.u32 %8, 0, 0;"
+        : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]), "+r"(acc[6]),
+          "+r"(acc[7]), "=r"(c)
+        : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+    return c;
+}
+
+// same, when the bound on the running value proves there is no carry out
+__device__ __forceinline__ void mad_row(uint32_t (&acc)[8], uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3,
+                                        uint32_t y) {
+    asm("mad.lo.cc.u32 %0, %8, %12, %0;\n\t"
+        "madc.hi.cc.u32 %1, %8, %12, %1;\n\t"
+        "madc.lo.cc.u32 %2, %9, %12, %2;\n\t"
+        "madc.hi.cc.u32 %3, %9, %12, %3;\n\t"
+        "madc.lo.cc.u32 %4, %10, %12, %4;\n\t"
+        "madc.hi.cc.u32 %5, %10, %12, %5;\n\t"
+        "madc.lo.cc.u32 %6, %11, %12, %6;\n\t"
+        "madc.hi.u32 %7, %11, %12, %7;"
+        : "+r"(acc[0]), "+r"(acc[1]), "+r"(acc[2]), "+r"(acc[3]), "+r"(acc[4]), "+r"(acc[5]), "+r"(acc[6]),
+          "+r"(acc[7])
+        : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+}
+
+// out[0..7] = {x0..x3} * y (aligned pairs, no carries)
+__device__ __forceinline__ void mul_row(uint32_t (&out)[8], uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3,
+                                        uint32_t y) {
+    asm("mul.lo.u32 %0, %8, %12;\n\t"
+        "mul.hi.u32 %1, %8, %12;\n\t"
+        "mul.lo.u32 %2, %9, %12;\n\t"
+        "mul.hi.u32 %3, %9, %12;\n\t"
+        "mul.lo.u32 %4, %10, %12;\n\t"
+        "mul.hi.u32 %5, %10, %12;\n\t"
+        "mul.lo.u32 %6, %11, %12;\n\t"
+        "mul.hi.u32 %7, %11, %12;"
+        : "=r"(out[0]), "=r"(out[1]), "=r"(out[2]), "=r"(out[3]), "=r"(out[4]), "=r"(out[5]), "=r"(out[6]),
+          "=r"(out[7])
+        : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+}
+
+// The one-limb shift between rows, fused with the odd-limb products of the next row:
+//   lo0 += sh[1]                                  (carry goes on into limb 1 = out[0])
+//   out[j] = {x0..x3}*y on pairs + sh[j+2] + carry   (sh[8] = sh[9] = 0)
+__device__ __forceinline__ void mad_row_shift(uint32_t (&out)[8], uint32_t& lo0, const uint32_t (&sh)[8], uint32_t x0,
+                                              uint32_t x1, uint32_t x2, uint32_t x3, uint32_t y) {
+    asm("add.cc.u32 %8, %8, %9;\n\t"
+        "madc.lo.cc.u32 %0, %16, %20, %10;\n\t"
+        "madc.hi.cc.u32 %1, %16, %20, %11;\n\t"
+        "madc.lo.cc.u32 %2, %17, %20, %12;\n\t"
+        "madc.hi.cc.u32 %3, %17, %20, %13;\n\t"
+        "madc.lo.cc.u32 %4, %18, %20, %14;\n\t"
+        "madc.hi.cc.u32 %5, %18, %20, %15;\n\t"
+        "madc.lo.cc.u32 %6, %19, %20, 0;\n\t"
+        "madc.hi.u32 %7, %19, %20, 0;"
+        : "=&r"(out[0]), "=&r"(out[1]), "=&r"(out[2]), "=&r"(out[3]), "=&r"(out[4]), "=&r"(out[5]), "=&r"(out[6]),
+          "=&r"(out[7]), "+r"(lo0)
+        : "r"(sh[1]), "r"(sh[2]), "r"(sh[3]), "r"(sh[4]), "r"(sh[5]), "r"(sh[6]), "r"(sh[7]), "r"(x0), "r"(x1),
+          "r"(x2), "r"(x3), "r"(y));
+}
+
+template <class P>
+struct Field {
+    typedef fe_t el;
+
+    static __device__ __forceinline__ el zero() {
+        el r;
+#pragma unroll
+        for (int i = 0; i < 8; i++) r.v[i] = 0;
+        return r;
+    }
+    static __device__ __forceinline__ el one() {  // Montgomery form of 1
+        el r;
+#pragma unroll
+        for (int i = 0; i < 8; i++) r.v[i] = P::r1(i);
+        return r;
+    }
+    static __device__ __forceinline__ el r2() {
+        el r;
+#pragma unroll
+        for (int i = 0; i < 8; i++) r.v[i] = P::r2(i);
+        return r;
+    }
+    static __device__ __forceinline__ bool is_zero(const el& a) {
+        uint32_t o = a.v[0] | a.v[1] | a.v[2] | a.v[3] | a.v[4] | a.v[5] | a.v[6] | a.v[7];
+        return o == 0;
+    }
+    static __device__ __forceinline__ bool eq(const el& a, const el& b) {
+        uint32_t o = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) o |= a.v[i] ^ b.v[i];
+        return o == 0;
+    }
+
+    // r = a - MOD if a >= MOD (a < 2*MOD)
+    static __device__ __forceinline__ void final_sub(uint32_t (&r)[8]) {
+        uint32_t t[8], borrow;
+        asm("sub.cc.u32 %0, %9, %17;\n\t"
+            "subc.cc.u32 %1, %10, %18;\n\t"
+            "subc.cc.u32 %2, %11, %19;\n\t"
+            "subc.cc.u32 %3, %12, %20;\n\t"
+            "subc.cc.u32 %4, %13, %21;\n\t"
+            "subc.cc.u32 %5, %14, %22;\n\t"
+            "subc.cc.u32 %6, %15, %23;\n\t"
+            "subc.cc.u32 %7, %16, %24;\n\t"
+            "subc.u32 %8, 0, 0;"
+            : "=r"(t[0]), "=r"(t[1]), "=r"(t[2]), "=r"(t[3]), "=r"(t[4]), "=r"(t[5]), "=r"(t[6]), "=r"(t[7]),
+              "=r"(borrow)
+            : "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+              "r"(P::mod(0)), "r"(P::mod(1)), "r"(P::mod(2)), "r"(P::mod(3)), "r"(P::mod(4)), "r"(P::mod(5)),
+              "r"(P::mod(6)), "r"(P::mod(7)));
+        if (borrow == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) r[i] = t[i];
+        }
+    }
+
+    static __device__ __forceinline__ el add(const el& a, const el& b) {
+        uint32_t r[8];
+        asm("add.cc.u32 %0, %8, %16;\n\t"
+            "addc.cc.u32 %1, %9, %17;\n\t"
+            "addc.cc.u32 %2, %10, %18;\n\t"
+            "addc.cc.u32 %3, %11, %19;\n\t"
+            "addc.cc.u32 %4, %12, %20;\n\t"
+            "addc.cc.u32 %5, %13, %21;\n\t"
+            "addc.cc.u32 %6, %14, %22;\n\t"
+            "addc.u32 %7, %15, %23;"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+            : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+              "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+        final_sub(r);  // a + b < 2*MOD < 2^255: no carry out of limb 7
+        el o;
+#pragma unroll
+        for (int i = 0; i < 8; i++) o.v[i] = r[i];
+        return o;
+    }
+
+    static __device__ __forceinline__ el dbl(const el& a) { return add(a, a); }
+
+    static __device__ __forceinline__ el sub(const el& a, const el& b) {
+        uint32_t r[8], borrow;
+        asm("sub.cc.u32 %0, %9, %17;\n\t"
+            "subc.cc.u32 %1, %10, %18;\n\t"
+            "subc.cc.u32 %2, %11, %19;\n\t"
+            "subc.cc.u32 %3, %12, %20;\n\t"
+            "subc.cc.u32 %4, %13, %21;\n\t"
+            "subc.cc.u32 %5, %14, %22;\n\t"
+            "subc.cc.u32 %6, %15, %23;\n\t"
+            "subc.cc.u32 %7, %16, %24;\n\t"
+            "subc.u32 %8, 0, 0;"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(borrow)
+            : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+              "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+        // borrow is 0 or 0xffffffff: add MOD & borrow
+        asm("add.cc.u32 %0, %0, %8;\n\t"
+            "addc.cc.u32 %1, %1, %9;\n\t"
+            "addc.cc.u32 %2, %2, %10;\n\t"
+            "addc.cc.u32 %3, %3, %11;\n\t"
+            "addc.cc.u32 %4, %4, %12;\n\t"
+            "addc.cc.u32 %5, %5, %13;\n\t"
+            "addc.cc.u32 %6, %6, %14;\n\t"
+            "addc.u32 %7, %7, %15;"
+            : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7])
+            : "r"(P::mod(0) & borrow), "r"(P::mod(1) & borrow), "r"(P::mod(2) & borrow), "r"(P::mod(3) & borrow),
+              "r"(P::mod(4) & borrow), "r"(P::mod(5) & borrow), "r"(P::mod(6) & borrow), "r"(P::mod(7) & borrow));
+        el o;
+#pragma unroll
+        for (int i = 0; i < 8; i++) o.v[i] = r[i];
+        return o;
+    }
+
+    static __device__ __forceinline__ el neg(const el& a) {
+        if (is_zero(a)) return a;
+        el m;
+#pragma unroll
+        for (int i = 0; i < 8; i++) m.v[i] = P::mod(i);
+        return sub(m, a);
+    }
+
+    // Montgomery product a*b/R mod MOD; a < MOD, b < 2^256 (so raw witness bytes are a legal `b`)
+    static __device__ __forceinline__ el mul(const el& a, const el& b) {
+        uint32_t E[8], O[8], T[8];
+        // row 0
+        mul_row(E, a.v[0], a.v[2], a.v[4], a.v[6], b.v[0]);
+        mul_row(O, a.v[1], a.v[3], a.v[5], a.v[7], b.v[0]);
+        uint32_t m = E[0] * P::INV;
+        mad_row(O, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+        O[7] += mad_row_c(E, P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+#pragma unroll
+        for (int i = 1; i < 8; i++) {
+            // frame moves up one limb: new even accumulator = old odd one; old even one is shifted into T
+            mad_row_shift(T, O[0], E, a.v[1], a.v[3], a.v[5], a.v[7], b.v[i]);
+            T[7] += mad_row_c(O, a.v[0], a.v[2], a.v[4], a.v[6], b.v[i]);
+            m = O[0] * P::INV;
+            mad_row(T, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);
+            T[7] += mad_row_c(O, P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                E[k] = O[k];
+                O[k] = T[k];
+            }
+        }
+        // value = O + (E >> 32)   (E[0] == 0)
+        uint32_t r[8];
+        asm("add.cc.u32 %0, %8, %16;\n\t"
+            "addc.cc.u32 %1, %9, %17;\n\t"
+            "addc.cc.u32 %2, %10, %18;\n\t"
+            "addc.cc.u32 %3, %11, %19;\n\t"
+            "addc.cc.u32 %4, %12, %20;\n\t"
+            "addc.cc.u32 %5, %13, %21;\n\t"
+            "addc.cc.u32 %6, %14, %22;\n\t"
+            "addc.u32 %7, %15, 0;"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+            : "r"(O[0]), "r"(O[1]), "r"(O[2]), "r"(O[3]), "r"(O[4]), "r"(O[5]), "r"(O[6]), "r"(O[7]), "r"(E[1]),
+              "r"(E[2]), "r"(E[3]), "r"(E[4]), "r"(E[5]), "r"(E[6]), "r"(E[7]));
+        final_sub(r);
+        el o;
+#pragma unroll
+        for (int k = 0; k < 8; k++) o.v[k] = r[k];
+        return o;
+    }
+
+    static __device__ __forceinline__ el sqr(const el& a) { return mul(a, a); }
+
+    static __device__ __forceinline__ el to_mont(const el& a) { return mul(r2(), a); }
+    static __device__ __forceinline__ el from_mont(const el& a) {
+        el o = zero();
+        o.v[0] = 1;
+        return mul(a, o);
+    }
+
+    // a^e, e given as 8 little-endian limbs (host constant); used for inversions off the hot path
+    static __device__ el pow(const el& a, const uint32_t (&e)[8]) {
+        el r = one();
+        for (int i = 255; i >= 0; i--) {
+            r = sqr(r);
+            if ((e[i >> 5] >> (i & 31)) & 1) r = mul(r, a);
+        }
+        return r;
+    }
+    static __device__ el inv(const el& a) {  // Fermat; inv(0) = 0
+        uint32_t e[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) e[i] = P::mod(i);
+        e[0] -= 2;  // MOD[0] >= 2 for both primes, no borrow
+        return pow(a, e);
+    }
+};
+
+typedef Field<FqParams> Fq;
+typedef Field<FrParams> Fr;
+
+// ---- Fq2 = Fq[u]/(u^2+1) (wasmcurves build_f2m, non-residue -1) ----------------------------------------
+struct alignas(16) fe2_t {
+    fe_t c0, c1;
+};
+
+struct Fq2 {
+    typedef fe2_t el;
+    static __device__ __forceinline__ el zero() { return el{Fq::zero(), Fq::zero()}; }
+    static __device__ __forceinline__ el one() { return el{Fq::one(), Fq::zero()}; }
+    static __device__ __forceinline__ bool is_zero(const el& a) { return Fq::is_zero(a.c0) && Fq::is_zero(a.c1); }
+    static __device__ __forceinline__ bool eq(const el& a, const el& b) { return Fq::eq(a.c0, b.c0) && Fq::eq(a.c1, b.c1); }
+    static __device__ __forceinline__ el add(const el& a, const el& b) { return el{Fq::add(a.c0, b.c0), Fq::add(a.c1, b.c1)}; }
+    static __device__ __forceinline__ el sub(const el& a, const el& b) { return el{Fq::sub(a.c0, b.c0), Fq::sub(a.c1, b.c1)}; }
+    static __device__ __forceinline__ el dbl(const el& a) { return el{Fq::dbl(a.c0), Fq::dbl(a.c1)}; }
+    static __device__ __forceinline__ el neg(const el& a) { return el{Fq::neg(a.c0), Fq::neg(a.c1)}; }
+    // Karatsuba: 3 base-field products
+    static __device__ __forceinline__ el mul(const el& a, const el& b) {
+        fe_t t0 = Fq::mul(a.c0, b.c0);
+        fe_t t1 = Fq::mul(a.c1, b.c1);
+        fe_t s = Fq::mul(Fq::add(a.c0, a.c1), Fq::add(b.c0, b.c1));
+        return el{Fq::sub(t0, t1), Fq::sub(Fq::sub(s, t0), t1)};
+    }
+    static __device__ el inv(const el& a) {  // conj(a) / (a0^2 + a1^2)
+        fe_t d = Fq::inv(Fq::add(Fq::sqr(a.c0), Fq::sqr(a.c1)));
+        return el{Fq::mul(a.c0, d), Fq::neg(Fq::mul(a.c1, d))};
+    }
+    // (a0+a1)(a0-a1) + 2 a0 a1 u : 2 base-field products
+    static __device__ __forceinline__ el sqr(const el& a) {
+        fe_t t = Fq::mul(a.c0, a.c1);
+        fe_t c0 = Fq::mul(Fq::add(a.c0, a.c1), Fq::sub(a.c0, a.c1));
+        return el{c0, Fq::dbl(t)};
+    }
+};
+
+// 32-byte element load/store as two 16-byte vector accesses
+__device__ __forceinline__ fe_t ld_fe(const fe_t* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = q[0], b = q[1];
+    fe_t r;
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+    r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    return r;
+}
+__device__ __forceinline__ fe_t ldg_fe(const fe_t* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    fe_t r;
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w;
+    r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    return r;
+}
+__device__ __forceinline__ void st_fe(fe_t* p, const fe_t& r) {
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = make_uint4(r.v[0], r.v[1], r.v[2], r.v[3]);
+    q[1] = make_uint4(r.v[4], r.v[5], r.v[6], r.v[7]);
+}
+
+}  // namespace g16

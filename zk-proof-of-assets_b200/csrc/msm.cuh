@@ -1,0 +1,495 @@
+// Pippenger multi-scalar multiplication over BN254 G1/G2 for sm_100a.
+//
+// Replaces: ffjavascript 0.2.62 engine_multiexp.js -> wasmcurves g1m/g2m_multiexpAffine_chunk,
+// rapidsnark multiexp.cpp (G1.multiMulByScalar / G2.multiMulByScalar); reference call site scripts/g16_prove.sh:246-260.
+// Inputs are the zkey's own records: affine Montgomery bases (64 B G1, 128 B G2; all-zero = infinity) and 32-byte
+// little-endian standard-form scalars (wtns section 2, or the H scalars from the NTT pipeline).
+//
+// Pipeline of one MSM (all on one stream; two tiny device->host reads of counters):
+//   digits   : signed c-bit windows per scalar; only non-zero digits become (bucket key, point index|sign) entries
+//   sort     : cub radix sort of the entries by key = window * 2^(c-1) + (|digit| - 1)
+//   bounds   : run start/end per bucket from the sorted keys
+//   tasks    : a bucket with more than T entries is cut into tasks of <= T entries (load balance for
+//              witness-like scalars where one bucket can hold a quarter of all points); tasks sorted by length
+//   accumulate (the hot kernel, IMAD bound): one thread per task, XYZZ mixed additions, next point prefetched
+//   combine  : buckets that were cut are summed by one CTA each
+//   reduce   : per chunk of L buckets a running-sum gives sum (b+1) B_b; chunks are tree-summed per window
+//   windows  : Horner over the W window sums (c doublings each)
+#pragma once
+#include <cub/cub.cuh>
+#include <stdexcept>
+#include <string>
+#include "common.cuh"
+#include "curve.cuh"
+
+namespace g16 {
+
+static inline int msm_num_windows(int c) { return (255 + c - 1) / c; }
+
+// heuristic window width: bucket reduction (2 full adds per bucket per window) stays a few % of accumulation
+static inline int msm_pick_c(size_t n) {
+    int lg = 0;
+    while ((size_t(1) << (lg + 1)) <= n) lg++;
+    int c = lg - 5;
+    if (c < 6) c = 6;
+    if (c > 20) c = 20;
+    return c;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// digits
+// ---------------------------------------------------------------------------------------------------------
+// scalars: n x 8 u32 (standard form, < 2^254).  inf_mask: optional bitmask, bit i set = base i is infinity.
+static __global__ void msm_digits_kernel(const uint32_t* __restrict__ scalars, uint32_t n, const uint32_t* __restrict__ inf_mask,
+                                  int c, int W, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                  unsigned long long* __restrict__ counter) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t half = 1u << (c - 1);
+    const uint32_t mask = (1u << c) - 1;
+    uint32_t cnt = 0;
+    uint32_t s[8];
+    bool live = i < n;
+    if (live && inf_mask && ((inf_mask[i >> 5] >> (i & 31)) & 1)) live = false;
+    if (live) {
+        const uint4* p = reinterpret_cast<const uint4*>(scalars + size_t(i) * 8);
+        uint4 a = p[0], b = p[1];
+        s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+        if ((s[0] | s[1] | s[2] | s[3] | s[4] | s[5] | s[6] | s[7]) == 0) live = false;
+    }
+    // pass 1: count non-zero signed digits
+    if (live) {
+        uint32_t carry = 0;
+        for (int w = 0; w < W; w++) {
+            int bit = w * c, limb = bit >> 5, sh = bit & 31;
+            unsigned long long v = limb < 8 ? s[limb] : 0;
+            if (limb + 1 < 8) v |= (unsigned long long)s[limb + 1] << 32;
+            uint32_t d = (uint32_t)((v >> sh) & mask) + carry;
+            carry = d > half;
+            if (d != 0 && d != (1u << c)) cnt++;  // d == 2^c becomes digit 0 with a carry
+        }
+    }
+    // warp-aggregated reservation of output slots
+    uint32_t lane = threadIdx.x & 31;
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    unsigned long long base = 0;
+    if (lane == 31 && total) base = atomicAdd(counter, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    if (!live || cnt == 0) return;
+    unsigned long long pos = base + (incl - cnt);
+    uint32_t carry = 0;
+    for (int w = 0; w < W; w++) {
+        int bit = w * c, limb = bit >> 5, sh = bit & 31;
+        unsigned long long v = limb < 8 ? s[limb] : 0;
+        if (limb + 1 < 8) v |= (unsigned long long)s[limb + 1] << 32;
+        uint32_t d = (uint32_t)((v >> sh) & mask) + carry;
+        carry = d > half;
+        if (d == 0 || d == (1u << c)) continue;
+        uint32_t neg = carry;
+        uint32_t mag = neg ? (1u << c) - d : d;  // 1 .. half
+        keys[pos] = (uint32_t)w * half + (mag - 1);
+        vals[pos] = i | (neg << 31);
+        pos++;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// bucket bounds and tasks
+// ---------------------------------------------------------------------------------------------------------
+static __global__ void msm_bounds_kernel(const uint32_t* __restrict__ keys, uint32_t m, uint32_t* __restrict__ start,
+                                  uint32_t* __restrict__ end) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    uint32_t k = keys[i];
+    if (i == 0 || keys[i - 1] != k) start[k] = i;
+    if (i == m - 1 || keys[i + 1] != k) end[k] = i + 1;
+}
+
+// per bucket: number of tasks, number of partial-sum slots (0 unless the bucket is cut), list of cut buckets
+static __global__ void msm_count_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end, uint32_t nb,
+                                       uint32_t T, uint32_t* __restrict__ ntasks, uint32_t* __restrict__ nparts,
+                                       uint32_t* __restrict__ cut_list, uint32_t* __restrict__ cut_count) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > nb) return;
+    uint32_t t = 0;
+    if (k < nb) t = (end[k] - start[k] + T - 1) / T;
+    ntasks[k] = t;
+    nparts[k] = t > 1 ? t : 0;
+    if (t > 1) cut_list[atomicAdd(cut_count, 1u)] = k;
+}
+
+// task j -> (first entry, length, output slot); slot bit 31 set = partial-sum array, else bucket array
+static __global__ void msm_make_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end,
+                                      const uint32_t* __restrict__ task_base, const uint32_t* __restrict__ part_base,
+                                      uint32_t nb, uint32_t nt, uint32_t T, uint32_t* __restrict__ t_begin,
+                                      uint32_t* __restrict__ t_len, uint32_t* __restrict__ t_out,
+                                      uint32_t* __restrict__ sort_key, uint32_t* __restrict__ sort_val) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nt) return;
+    // last k with task_base[k] <= j  (task_base has nb+1 entries, non-decreasing, task_base[nb] = nt)
+    uint32_t lo = 0, hi = nb;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi + 1) >> 1;
+        if (task_base[mid] <= j) lo = mid;
+        else hi = mid - 1;
+    }
+    uint32_t k = lo;
+    uint32_t local = j - task_base[k];
+    uint32_t b = start[k] + local * T;
+    uint32_t len = min(T, end[k] - b);
+    uint32_t nt_k = task_base[k + 1] - task_base[k];
+    t_begin[j] = b;
+    t_len[j] = len;
+    t_out[j] = nt_k > 1 ? (0x80000000u | (part_base[k] + local)) : k;
+    sort_key[j] = T - len;  // longest tasks first
+    sort_val[j] = j;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// accumulate: the hot kernel
+// ---------------------------------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t* __restrict__ vals,
+                      const uint32_t* __restrict__ order, const uint32_t* __restrict__ t_begin,
+                      const uint32_t* __restrict__ t_len, const uint32_t* __restrict__ t_out, uint32_t nt,
+                      typename C::pt* __restrict__ buckets, typename C::pt* __restrict__ parts) {
+    typedef typename C::aff aff;
+    typedef typename C::pt pt;
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= nt) return;
+    uint32_t j = order[tid];
+    uint32_t e = t_begin[j], len = t_len[j], out = t_out[j];
+    pt acc = C::identity();
+    uint32_t v = vals[e];
+    aff q = bases[v & 0x7fffffffu];
+    for (uint32_t k = 0; k < len; k++) {
+        uint32_t vn = 0;
+        aff qn = q;
+        if (k + 1 < len) {  // prefetch the next point while this one is added
+            vn = vals[e + k + 1];
+            qn = bases[vn & 0x7fffffffu];
+        }
+        if (v >> 31) q.y = C::field::neg(q.y);
+        C::madd(acc, q);
+        v = vn;
+        q = qn;
+    }
+    if (out >> 31) parts[out & 0x7fffffffu] = acc;
+    else buckets[out] = acc;
+}
+
+// block-wide tree sum of XYZZ points held one per thread; result in thread 0
+template <class C, int THREADS>
+__device__ __forceinline__ void block_sum_points(typename C::pt& acc, typename C::pt* sh) {
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = THREADS / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) {
+            typename C::pt a = sh[threadIdx.x];
+            C::add(a, sh[threadIdx.x + s]);
+            sh[threadIdx.x] = a;
+        }
+        __syncthreads();
+    }
+    acc = sh[0];
+}
+
+// one CTA per cut bucket: sum its partial sums
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+msm_combine_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __restrict__ part_base,
+                   const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ buckets) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    typename C::pt* sh = reinterpret_cast<typename C::pt*>(smem_raw);
+    uint32_t k = cut_list[blockIdx.x];
+    uint32_t b = part_base[k], e = part_base[k + 1];
+    typename C::pt acc = C::identity();
+    for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts[i]);
+    block_sum_points<C, THREADS>(acc, sh);
+    if (threadIdx.x == 0) buckets[k] = acc;
+}
+
+// thread per chunk of L buckets of one window: out = sum_{b in chunk} (b+1) * B_b
+template <class C>
+__global__ void __launch_bounds__(64)
+msm_chunk_reduce_kernel(const typename C::pt* __restrict__ buckets, uint32_t buckets_per_window, uint32_t L,
+                        uint32_t chunks_per_window, uint32_t nchunks, typename C::pt* __restrict__ chunk_out) {
+    typedef typename C::pt pt;
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nchunks) return;
+    uint32_t w = t / chunks_per_window, ch = t % chunks_per_window;
+    uint32_t lo = ch * L;
+    uint32_t hi = min(lo + L, buckets_per_window);
+    const pt* B = buckets + size_t(w) * buckets_per_window;
+    pt run = C::identity(), acc = C::identity();
+    for (uint32_t b = hi; b-- > lo;) {
+        C::add(run, B[b]);
+        C::add(acc, run);
+    }
+    if (lo) {
+        pt s = C::mul_small(run, lo);
+        C::add(acc, s);
+    }
+    chunk_out[t] = acc;
+}
+
+// one CTA per window: tree-sum its chunk results
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+msm_window_sum_kernel(const typename C::pt* __restrict__ chunk_out, uint32_t chunks_per_window,
+                      typename C::pt* __restrict__ window_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    typename C::pt* sh = reinterpret_cast<typename C::pt*>(smem_raw);
+    const typename C::pt* p = chunk_out + size_t(blockIdx.x) * chunks_per_window;
+    typename C::pt acc = C::identity();
+    for (uint32_t i = threadIdx.x; i < chunks_per_window; i += THREADS) C::add(acc, p[i]);
+    block_sum_points<C, THREADS>(acc, sh);
+    if (threadIdx.x == 0) window_out[blockIdx.x] = acc;
+}
+
+// Horner over windows: result = sum_w 2^(c w) S_w
+template <class C>
+__global__ void msm_horner_kernel(const typename C::pt* __restrict__ window_out, int W, int c,
+                                  typename C::pt* __restrict__ result) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    typename C::pt acc = window_out[W - 1];
+    for (int w = W - 2; w >= 0; w--) {
+        for (int i = 0; i < c; i++) acc = C::dbl(acc);
+        C::add(acc, window_out[w]);
+    }
+    *result = acc;
+}
+
+// bit i of mask = base i is the all-zero record (infinity)
+template <class C>
+__global__ void msm_inf_mask_kernel(const typename C::aff* __restrict__ bases, uint32_t n, uint32_t* __restrict__ mask) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool inf = i < n ? C::is_inf(bases[i]) : true;
+    uint32_t bits = __ballot_sync(0xffffffffu, inf);
+    if ((threadIdx.x & 31) == 0 && i < n) mask[i >> 5] = bits;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side: workspace + staged launch
+// ---------------------------------------------------------------------------------------------------------
+struct MsmConfig {
+    int c = 0;          // window bits (0 = pick from n)
+    uint32_t T = 0;     // max entries per task (0 = 4 x mean bucket load, at least 32)
+    uint32_t L = 16;    // buckets per reduction chunk
+};
+
+// Counters a finished MSM leaves behind (for bench.py's work model and tests)
+struct MsmStats {
+    unsigned long long entries = 0;  // non-zero digits = mixed additions issued
+    uint32_t tasks = 0, cut_buckets = 0, buckets = 0;
+    int c = 0, W = 0;
+};
+
+template <class C>
+class Msm {
+public:
+    typedef typename C::aff aff;
+    typedef typename C::pt pt;
+
+    Msm() {}
+    ~Msm() {
+        if (h_counters) cudaFreeHost(h_counters);
+        if (h_result) cudaFreeHost(h_result);
+    }
+
+    // capacity for n points
+    void reserve(size_t n, const MsmConfig& cfg_in = MsmConfig()) {
+        cfg = cfg_in;
+        cap_n = n;
+        c = cfg.c ? cfg.c : msm_pick_c(n);
+        W = msm_num_windows(c);
+        bpw = 1u << (c - 1);
+        nb = uint32_t(W) * bpw;
+        size_t m_max = n * size_t(W);
+        if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
+        T = cfg.T;
+        if (T == 0) {
+            size_t mean = n / bpw + 1;
+            T = uint32_t(mean * 4 < 32 ? 32 : mean * 4);
+        }
+        L = cfg.L;
+        cpw = (bpw + L - 1) / L;
+        size_t nt_max = nb + m_max / T + 2;
+        size_t np_max = 2 * (m_max / T) + 2;
+        size_t e = m_max ? m_max : 1;
+        keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_a.alloc(e * 4); vals_b.alloc(e * 4);
+        start.alloc(size_t(nb) * 4); end.alloc(size_t(nb) * 4);
+        ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4);
+        task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4);
+        cut_list.alloc((m_max / T + 2) * 4);
+        t_begin.alloc(nt_max * 4); t_len.alloc(nt_max * 4); t_out.alloc(nt_max * 4);
+        tk_a.alloc(nt_max * 4); tk_b.alloc(nt_max * 4); tv_a.alloc(nt_max * 4); tv_b.alloc(nt_max * 4);
+        buckets.alloc(size_t(nb) * sizeof(pt));
+        parts.alloc(np_max * sizeof(pt));
+        chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
+        window_out.alloc(size_t(W) * sizeof(pt));
+        result.alloc(sizeof(pt));
+        counters.alloc(64);
+        // cub temp: max over the calls we make
+        size_t t1 = 0, t2 = 0, t3 = 0;
+        cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
+        cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
+        cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)e, 0, key_bits());
+        cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
+        cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
+        cub::DeviceRadixSort::SortPairs(nullptr, t2, tk, tv, (int)nt_max, 0, 32);
+        cub::DeviceScan::ExclusiveSum(nullptr, t3, ntasks.as<uint32_t>(), task_base.as<uint32_t>(), (int)(nb + 1));
+        size_t t = t1 > t2 ? t1 : t2;
+        if (t3 > t) t = t3;
+        cub_tmp.alloc(t + 256);
+        if (!h_counters) G16_CUDA(cudaMallocHost(&h_counters, 64));
+        if (!h_result) G16_CUDA(cudaMallocHost(&h_result, sizeof(pt)));
+    }
+
+    size_t workspace_bytes() const {
+        return keys_a.bytes * 4 + start.bytes * 6 + t_begin.bytes * 7 + buckets.bytes + parts.bytes + chunk_out.bytes +
+               cub_tmp.bytes;
+    }
+
+    // stage 1: digits (async).  scalars/bases/mask are device pointers; n <= reserved capacity.
+    void stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
+        if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
+        bases = bases_;
+        n = n_;
+        stream = s;
+        G16_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
+        if (n) {
+            msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, W,
+                                                                          keys_a.as<uint32_t>(), vals_a.as<uint32_t>(),
+                                                                          counters.as<unsigned long long>());
+            G16_CUDA(cudaGetLastError());
+        }
+        G16_CUDA(cudaMemcpyAsync(h_counters, counters.p, 16, cudaMemcpyDeviceToHost, s));
+    }
+
+    // stage 2: sort + tasks (reads the entry count -> one stream sync)
+    void stage2() {
+        cudaStream_t s = stream;
+        G16_CUDA(cudaStreamSynchronize(s));
+        m = (size_t)h_counters[0];
+        stats = MsmStats();
+        stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb;
+        G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
+        if (m == 0) return;
+        cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
+        cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
+        size_t tb = cub_tmp.bytes;
+        G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, dk, dv, (int)m, 0, key_bits(), s));
+        sorted_keys = dk.Current();
+        sorted_vals = dv.Current();
+        G16_CUDA(cudaMemsetAsync(start.p, 0, size_t(nb) * 4, s));
+        G16_CUDA(cudaMemsetAsync(end.p, 0, size_t(nb) * 4, s));
+        msm_bounds_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s>>>(sorted_keys, (uint32_t)m, start.as<uint32_t>(),
+                                                                      end.as<uint32_t>());
+        uint32_t* cut_count = counters.as<uint32_t>() + 4;  // byte offset 16
+        msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb, T,
+                                                                    ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
+                                                                    cut_list.as<uint32_t>(), cut_count);
+        tb = cub_tmp.bytes;
+        G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, ntasks.as<uint32_t>(), task_base.as<uint32_t>(),
+                                               (int)(nb + 1), s));
+        tb = cub_tmp.bytes;
+        G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, nparts.as<uint32_t>(), part_base.as<uint32_t>(),
+                                               (int)(nb + 1), s));
+        // h_counters[2] = number of tasks, [3] = number of cut buckets
+        G16_CUDA(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h_counters) + 4, task_base.as<uint32_t>() + nb, 4,
+                                 cudaMemcpyDeviceToHost, s));
+        G16_CUDA(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h_counters) + 5, cut_count, 4, cudaMemcpyDeviceToHost, s));
+    }
+
+    // stage 3: accumulate + reductions (reads the task count -> one stream sync); result stays on the device
+    void stage3() {
+        cudaStream_t s = stream;
+        if (m != 0) {
+            G16_CUDA(cudaStreamSynchronize(s));
+            uint32_t nt = reinterpret_cast<uint32_t*>(h_counters)[4];
+            uint32_t ncut = reinterpret_cast<uint32_t*>(h_counters)[5];
+            stats.tasks = nt;
+            stats.cut_buckets = ncut;
+            msm_make_tasks_kernel<<<(nt + 255) / 256, 256, 0, s>>>(
+                start.as<uint32_t>(), end.as<uint32_t>(), task_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, nt, T,
+                t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), tk_a.as<uint32_t>(),
+                tv_a.as<uint32_t>());
+            cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
+            cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
+            size_t tb = cub_tmp.bytes;
+            int bits = 1;
+            while ((1u << bits) <= T) bits++;
+            G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
+            msm_accumulate_kernel<C><<<(nt + 127) / 128, 128, 0, s>>>(
+                bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
+                buckets.as<pt>(), parts.as<pt>());
+            G16_CUDA(cudaGetLastError());
+            if (ncut) {
+                msm_combine_kernel<C, RED_THREADS><<<ncut, RED_THREADS, RED_THREADS * sizeof(pt), s>>>(
+                    cut_list.as<uint32_t>(), part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
+                G16_CUDA(cudaGetLastError());
+            }
+        }
+        uint32_t nchunks = uint32_t(W) * cpw;
+        msm_chunk_reduce_kernel<C><<<(nchunks + 63) / 64, 64, 0, s>>>(buckets.as<pt>(), bpw, L, cpw, nchunks,
+                                                                      chunk_out.as<pt>());
+        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, RED_THREADS * sizeof(pt), s>>>(chunk_out.as<pt>(), cpw,
+                                                                                              window_out.as<pt>());
+        msm_horner_kernel<C><<<1, 32, 0, s>>>(window_out.as<pt>(), W, c, result.as<pt>());
+        G16_CUDA(cudaGetLastError());
+        G16_CUDA(cudaMemcpyAsync(h_result, result.p, sizeof(pt), cudaMemcpyDeviceToHost, s));
+    }
+
+    // whole MSM on one stream; returns after the result is in host memory
+    const pt* run(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
+        stage1(bases_, scalars, inf_mask, n_, s);
+        stage2();
+        stage3();
+        G16_CUDA(cudaStreamSynchronize(s));
+        return h_result;
+    }
+    const pt* host_result() const { return h_result; }  // valid after the stream is synchronised
+    const pt* device_result() const { return result.as<pt>(); }
+    static void prepare() {  // opt in to > 48 KB dynamic shared memory for the G2 reductions
+        cudaFuncSetAttribute(msm_combine_kernel<C, RED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(RED_THREADS * sizeof(pt)));
+        cudaFuncSetAttribute(msm_window_sum_kernel<C, RED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(RED_THREADS * sizeof(pt)));
+    }
+
+    MsmStats stats;
+    int c = 0, W = 0;
+    uint32_t T = 0, L = 0;
+
+private:
+    static constexpr int RED_THREADS = 128;
+    int key_bits() const {
+        int b = 1;
+        while ((size_t(1) << b) < nb) b++;
+        return b;
+    }
+    MsmConfig cfg;
+    size_t cap_n = 0, n = 0, m = 0;
+    uint32_t bpw = 0, nb = 0, cpw = 0;
+    const aff* bases = nullptr;
+    cudaStream_t stream = 0;
+    uint32_t *sorted_keys = nullptr, *sorted_vals = nullptr;
+    DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, task_base, part_base, cut_list, t_begin, t_len,
+        t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, chunk_out, window_out, result, counters, cub_tmp;
+    unsigned long long* h_counters = nullptr;
+    pt* h_result = nullptr;
+};
+
+#ifndef G16_MSM_INSTANTIATE
+extern template class Msm<G1>;
+extern template class Msm<G2>;
+#endif
+
+}  // namespace g16

@@ -1,0 +1,224 @@
+// Radix-2 NTT passes over Fr and the H-polynomial pipeline  P = (A.B - C) on the odd coset.
+//
+// Replaces: ffjavascript 0.2.62 engine_fft.js / engine_applykey.js (Fr.ifft, Fr.batchApplyKey,
+// Fr.fft), snarkjs 0.7.2 groth16_prove.js joinABC + batchFromMontgomery, rapidsnark FFT<Fr>::ifft/fft; reference call
+// site scripts/g16_prove.sh:246-260.  Roots follow ffjavascript: w[28] = 5^((r-1)/2^28), w[k] = w[k+1]^2,
+// inc = w[log2 n + 1].
+//
+// Order trick: the inverse transform runs decimation-in-frequency (natural in, bit-reversed out), the coset shift
+// inc^i / n is applied in bit-reversed positions from a table as that transform's last pass stores, and the forward
+// transform runs decimation-in-time (bit-reversed in, natural out) -- no bit-reversal pass exists.
+//
+// A transform of 2^logn points is ceil(logn/10) passes; a pass stages up to 10 butterfly levels of a 1024-element
+// tile in shared memory (32 KB) and makes one coalesced round trip to HBM.  Index math prototyped in
+// scratch/nttsim.py against the oracle.
+#pragma once
+#include <vector>
+#include "common.cuh"
+#include "field.cuh"
+#include "hostfield.hpp"
+
+namespace g16 {
+
+constexpr int NTT_TILE_LOG = 10;
+constexpr int NTT_TILE = 1 << NTT_TILE_LOG;
+constexpr int NTT_THREADS = 256;
+
+// a: data (Montgomery form).  tw[e] = w^e, e < n/2.  scale: optional per-position factor applied when storing.
+template <bool DIF, bool INV>
+__global__ void __launch_bounds__(NTT_THREADS)
+ntt_pass_kernel(fe_t* __restrict__ a, int logn, int s_lo, int k, const fe_t* __restrict__ tw,
+                const fe_t* __restrict__ scale) {
+    __shared__ fe_t sh[NTT_TILE];
+    const uint32_t n = 1u << logn;
+    const uint32_t nq = n >> k;                 // sub-transforms of 2^k points, stride 2^s_lo
+    const uint32_t S = NTT_TILE >> k;           // sub-transforms per tile
+    const uint32_t q0 = blockIdx.x * S;
+    const uint32_t Sq = min(S, nq - q0);
+    const uint32_t lomask = (1u << s_lo) - 1;
+
+    // load: shared layout follows the (coalesced) global order
+    for (uint32_t e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {
+        uint32_t qi, t;
+        if (s_lo > 0) { qi = e & (S - 1); t = e >> (NTT_TILE_LOG - k); }
+        else { t = e & ((1u << k) - 1); qi = e >> k; }
+        if (qi < Sq) {
+            uint32_t q = q0 + qi;
+            size_t idx = (size_t(q >> s_lo) << (s_lo + k)) + (size_t(t) << s_lo) + (q & lomask);
+            sh[e] = ld_fe(a + idx);
+        }
+    }
+    __syncthreads();
+
+    for (int step = 0; step < k; step++) {
+        const int r = DIF ? (k - 1 - step) : step;
+        const int b = s_lo + r;
+        for (uint32_t u = threadIdx.x; u < NTT_TILE / 2; u += NTT_THREADS) {
+            uint32_t qi, tp;
+            if (s_lo > 0) { qi = u & (S - 1); tp = u >> (NTT_TILE_LOG - k); }
+            else { tp = u & ((1u << (k - 1)) - 1); qi = u >> (k - 1); }
+            if (qi >= Sq) continue;
+            uint32_t tl = tp & ((1u << r) - 1), th = tp >> r;
+            uint32_t t0 = (th << (r + 1)) | tl;
+            uint32_t t1 = t0 + (1u << r);
+            uint32_t lo = (q0 + qi) & lomask;
+            uint32_t j = (tl << s_lo) + lo;
+            uint32_t ex = j << (logn - 1 - b);
+            uint32_t e0 = s_lo > 0 ? (t0 << (NTT_TILE_LOG - k)) + qi : (qi << k) + t0;
+            uint32_t e1 = s_lo > 0 ? (t1 << (NTT_TILE_LOG - k)) + qi : (qi << k) + t1;
+            fe_t x = sh[e0], y = sh[e1];
+            fe_t w;
+            bool unit = (ex == 0);
+            if (!unit) {
+                if (INV) w = Fr::neg(ldg_fe(tw + ((n >> 1) - ex)));
+                else w = ldg_fe(tw + ex);
+            }
+            if (DIF) {
+                fe_t d = Fr::sub(x, y);
+                sh[e0] = Fr::add(x, y);
+                sh[e1] = unit ? d : Fr::mul(d, w);
+            } else {
+                if (!unit) y = Fr::mul(y, w);
+                sh[e0] = Fr::add(x, y);
+                sh[e1] = Fr::sub(x, y);
+            }
+        }
+        __syncthreads();
+    }
+
+    for (uint32_t e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {
+        uint32_t qi, t;
+        if (s_lo > 0) { qi = e & (S - 1); t = e >> (NTT_TILE_LOG - k); }
+        else { t = e & ((1u << k) - 1); qi = e >> k; }
+        if (qi < Sq) {
+            uint32_t q = q0 + qi;
+            size_t idx = (size_t(q >> s_lo) << (s_lo + k)) + (size_t(t) << s_lo) + (q & lomask);
+            fe_t v = sh[e];
+            if (scale) v = Fr::mul(v, ldg_fe(scale + idx));
+            st_fe(a + idx, v);
+        }
+    }
+}
+
+// out[i] = prod over set bits b of i (or of bitrev(i)) of pw[b], times `mult`.  pw[b] = base^(2^b) (Montgomery).
+static __global__ void ntt_powers_kernel(fe_t* __restrict__ out, uint32_t count, int bits, bool bitrev,
+                                  const fe_t* __restrict__ pw, fe_t mult) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint32_t e = bitrev ? (bits ? __brev(i) >> (32 - bits) : 0) : i;
+    fe_t r = mult;
+    for (int b = 0; b < bits; b++)
+        if ((e >> b) & 1) r = Fr::mul(r, pw[b]);
+    st_fe(out + i, r);
+}
+
+// P[i] = from_montgomery(A[i]*B[i] - C[i])  (rows a8: joinABC + batchFromMontgomery)
+static __global__ void ntt_join_kernel(const fe_t* __restrict__ A, const fe_t* __restrict__ B, const fe_t* __restrict__ C,
+                                fe_t* __restrict__ P, uint32_t n) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    fe_t v = Fr::sub(Fr::mul(ld_fe(A + i), ld_fe(B + i)), ld_fe(C + i));
+    st_fe(P + i, Fr::from_mont(v));
+}
+
+inline std::vector<int> ntt_plan(int logn) {
+    int np = (logn + NTT_TILE_LOG - 1) / NTT_TILE_LOG;
+    if (np < 1) np = 1;
+    std::vector<int> ks(np);
+    for (int i = 0; i < np; i++) ks[i] = logn / np + (i < logn % np ? 1 : 0);
+    return ks;
+}
+
+// Per-domain tables, built once (zkey open) and kept resident.
+struct NttDomain {
+    int logn = 0;
+    DevBuf tw;     // w^e, e < max(1, n/2)
+    DevBuf scale;  // inc^bitrev(p) / n
+
+    static g16h::U256 root_of_unity(int log) {  // ffjavascript F1Field: w[28] = 5^((r-1)/2^28), squared down
+        using namespace g16h;
+        U256 e = HFr::mod();
+        e.v[0] -= 1;
+        // (r-1) >> 28
+        for (int i = 0; i < 4; i++) e.v[i] = (e.v[i] >> 28) | (i < 3 ? e.v[i + 1] << 36 : 0);
+        U256 w = HFr::pow(HFr::from_u64(5), e);
+        for (int i = 28; i > log; i--) w = HFr::sqr(w);
+        return w;  // Montgomery form
+    }
+
+    void init(int logn_, cudaStream_t s) {
+        using namespace g16h;
+        logn = logn_;
+        if (logn < 1 || logn > 28) throw std::runtime_error("NTT domain must be 2^1 .. 2^28");
+        size_t n = size_t(1) << logn;
+        tw.alloc((n / 2 ? n / 2 : 1) * sizeof(fe_t));
+        scale.alloc(n * sizeof(fe_t));
+        U256 w = root_of_unity(logn);
+        // row a6: inc = w[logn + 1]; for logn == 28 ffjavascript uses Fr.shift = nqr^2 = 25
+        U256 inc = logn < 28 ? root_of_unity(logn + 1) : HFr::from_u64(25);
+        U256 ninv = HFr::inv(HFr::from_u64(uint64_t(n)));
+        fe_t pw[64];
+        U256 a = w, b = inc;
+        for (int i = 0; i < 32; i++) {
+            std::memcpy(&pw[i], a.v, 32);
+            std::memcpy(&pw[32 + i], b.v, 32);
+            a = HFr::sqr(a);
+            b = HFr::sqr(b);
+        }
+        DevBuf dpw;
+        dpw.alloc(sizeof(pw));
+        G16_CUDA(cudaMemcpyAsync(dpw.p, pw, sizeof(pw), cudaMemcpyHostToDevice, s));
+        fe_t one_m, ninv_m;
+        U256 o = HFr::one();
+        std::memcpy(&one_m, o.v, 32);
+        std::memcpy(&ninv_m, ninv.v, 32);
+        uint32_t half = (uint32_t)(n / 2 ? n / 2 : 1);
+        ntt_powers_kernel<<<(half + 255) / 256, 256, 0, s>>>(tw.as<fe_t>(), half, logn - 1, false, dpw.as<fe_t>(), one_m);
+        ntt_powers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scale.as<fe_t>(), (uint32_t)n, logn, true,
+                                                                      dpw.as<fe_t>() + 32, ninv_m);
+        G16_CUDA(cudaGetLastError());
+        G16_CUDA(cudaStreamSynchronize(s));
+    }
+
+    // evaluations on the domain (natural order) -> evaluations on the odd coset (natural order), in place
+    void to_odd_coset(fe_t* a, cudaStream_t s) const {
+        std::vector<int> ks = ntt_plan(logn);
+        unsigned grid = (unsigned)(((size_t(1) << logn) + NTT_TILE - 1) / NTT_TILE);
+        int sl = logn;
+        for (size_t i = 0; i < ks.size(); i++) {
+            sl -= ks[i];
+            ntt_pass_kernel<true, true><<<grid, NTT_THREADS, 0, s>>>(a, logn, sl, ks[i], tw.as<fe_t>(),
+                                                                       sl == 0 ? scale.as<fe_t>() : nullptr);
+        }
+        sl = 0;
+        for (size_t i = ks.size(); i-- > 0;) {
+            ntt_pass_kernel<false, false><<<grid, NTT_THREADS, 0, s>>>(a, logn, sl, ks[i], tw.as<fe_t>(), nullptr);
+            sl += ks[i];
+        }
+        G16_CUDA(cudaGetLastError());
+    }
+
+    // plain transforms (test hooks / standalone operator): natural order in and out is NOT provided by a single call;
+    // forward_dit expects bit-reversed input, inverse_dif leaves bit-reversed output (unscaled).
+    void inverse_dif(fe_t* a, bool with_scale, cudaStream_t s) const {
+        std::vector<int> ks = ntt_plan(logn);
+        unsigned grid = (unsigned)(((size_t(1) << logn) + NTT_TILE - 1) / NTT_TILE);
+        int sl = logn;
+        for (size_t i = 0; i < ks.size(); i++) {
+            sl -= ks[i];
+            ntt_pass_kernel<true, true><<<grid, NTT_THREADS, 0, s>>>(
+                a, logn, sl, ks[i], tw.as<fe_t>(), (with_scale && sl == 0) ? scale.as<fe_t>() : nullptr);
+        }
+    }
+    void forward_dit(fe_t* a, cudaStream_t s) const {
+        std::vector<int> ks = ntt_plan(logn);
+        unsigned grid = (unsigned)(((size_t(1) << logn) + NTT_TILE - 1) / NTT_TILE);
+        int sl = 0;
+        for (size_t i = ks.size(); i-- > 0;) {
+            ntt_pass_kernel<false, false><<<grid, NTT_THREADS, 0, s>>>(a, logn, sl, ks[i], tw.as<fe_t>(), nullptr);
+            sl += ks[i];
+        }
+    }
+};
+
+}  // namespace g16

@@ -1,0 +1,803 @@
+// Groth16 prover: resident proving key, sparse R1CS evaluation, orchestration of the NTT pipeline and the five
+// MSMs, final combination and the proof.json / public.json writers.  C ABI in include/g16_b200.h.
+//
+// Replaces: snarkjs 0.7.2 src/groth16_prove.js + zkey_utils.js + wtns_utils.js,
+// rapidsnark Groth16::Prover::prove; reference call site scripts/g16_prove.sh:246-260.
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "../../include/g16_b200.h"
+#include "internal.cuh"
+
+using namespace g16;
+using namespace g16h;
+
+namespace g16 {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// iden3 binfile container (row a1): magic[4] | u32 version | u32 nSections | { u32 type | u64 size | payload }*
+// ---------------------------------------------------------------------------------------------------------
+struct Section {
+    const uint8_t* p = nullptr;
+    uint64_t size = 0;
+};
+
+struct FormatError : std::runtime_error {
+    explicit FormatError(const std::string& m) : std::runtime_error(m) {}
+};
+struct StatusError : std::runtime_error {
+    int code;
+    StatusError(int c, const std::string& m) : std::runtime_error(m), code(c) {}
+};
+
+static inline uint32_t rd32(const uint8_t* p) {
+    uint32_t v;
+    std::memcpy(&v, p, 4);
+    return v;
+}
+static inline uint64_t rd64(const uint8_t* p) {
+    uint64_t v;
+    std::memcpy(&v, p, 8);
+    return v;
+}
+
+static std::map<uint32_t, Section> parse_binfile(const uint8_t* data, size_t len, const char magic[4], uint32_t version) {
+    if (len < 12 || std::memcmp(data, magic, 4) != 0)
+        throw FormatError(std::string("Invalid File format: expected magic \"") + std::string(magic, 4) + "\"");
+    if (rd32(data + 4) > version) throw FormatError("Version not supported");
+    uint32_t nsec = rd32(data + 8);
+    std::map<uint32_t, Section> secs;
+    size_t pos = 12;
+    for (uint32_t i = 0; i < nsec; i++) {
+        if (pos + 12 > len) throw FormatError("binfile: truncated section header");
+        uint32_t typ = rd32(data + pos);
+        uint64_t size = rd64(data + pos + 4);
+        pos += 12;
+        if (size > len - pos) throw FormatError("binfile: section runs past the end of the file");
+        if (!secs.count(typ)) secs[typ] = Section{data + pos, size};
+        pos += size;
+    }
+    return secs;
+}
+
+static const Section& need(const std::map<uint32_t, Section>& secs, uint32_t typ, const char* what) {
+    auto it = secs.find(typ);
+    if (it == secs.end()) throw FormatError(std::string(what) + ": missing section " + std::to_string(typ));
+    return it->second;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// sparse R1CS evaluation (row a4, buildABC1): rows of A and B in CSR form, built once at key load
+// ---------------------------------------------------------------------------------------------------------
+struct __align__(4) CoefRec {  // zkey section 4 record, 44 bytes, unaligned for 16-byte loads
+    uint32_t m, c, s;
+    uint32_t value[8];
+};
+
+// key = m * n + c
+__global__ void r1cs_count_kernel(const uint8_t* __restrict__ recs, uint64_t ncoef, uint32_t n, uint32_t n_vars,
+                                  uint32_t* __restrict__ counts, uint32_t* __restrict__ bad) {
+    uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+    if (i >= ncoef) return;
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(recs + i * 44);
+    uint32_t m = r[0], c = r[1], s = r[2];
+    if (m > 1 || c >= n || s >= n_vars) {
+        atomicAdd(bad, 1u);
+        return;
+    }
+    atomicAdd(&counts[m * n + c], 1u);
+}
+
+__global__ void r1cs_fill_kernel(const uint8_t* __restrict__ recs, uint64_t ncoef, uint32_t n,
+                                 const uint32_t* __restrict__ row_ptr, uint32_t* __restrict__ cursor,
+                                 uint32_t* __restrict__ col, fe_t* __restrict__ val) {
+    uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+    if (i >= ncoef) return;
+    const uint32_t* r = reinterpret_cast<const uint32_t*>(recs + i * 44);
+    uint32_t key = r[0] * n + r[1];
+    uint32_t pos = row_ptr[key] + atomicAdd(&cursor[key], 1u);
+    col[pos] = r[2];
+    fe_t v;
+#pragma unroll
+    for (int k = 0; k < 8; k++) v.v[k] = r[3 + k];
+    st_fe(val + pos, v);
+}
+
+// thread per constraint row c: A[c] = sum coef (x) w[s], B[c] likewise, C[c] = A[c]*B[c].
+// coef is stored as coef*R^2 and w is the raw standard-form witness, so one Montgomery product gives coef*w in
+// Montgomery form (snarkjs buildABC1 does the same with frm_mul on the raw bytes).
+__global__ void __launch_bounds__(128)
+r1cs_eval_kernel(const uint32_t* __restrict__ row_ptr, const uint32_t* __restrict__ col, const fe_t* __restrict__ val,
+                 const fe_t* __restrict__ w, uint32_t n, fe_t* __restrict__ A, fe_t* __restrict__ B,
+                 fe_t* __restrict__ C) {
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    fe_t a = Fr::zero(), b = Fr::zero();
+    for (uint32_t p = row_ptr[c], e = row_ptr[c + 1]; p < e; p++)
+        a = Fr::add(a, Fr::mul(ld_fe(val + p), ldg_fe(w + col[p])));
+    for (uint32_t p = row_ptr[n + c], e = row_ptr[n + c + 1]; p < e; p++)
+        b = Fr::add(b, Fr::mul(ld_fe(val + p), ldg_fe(w + col[p])));
+    st_fe(A + c, a);
+    st_fe(B + c, b);
+    st_fe(C + c, Fr::mul(a, b));
+}
+
+}  // namespace g16
+
+// ---------------------------------------------------------------------------------------------------------
+// the resident proving key
+// ---------------------------------------------------------------------------------------------------------
+template <class C>
+struct BaseSection {
+    DevBuf bases;    // this shard's slice of the section
+    DevBuf mask;     // infinity bitmask
+    size_t lo = 0;   // first index of the slice within the section
+    size_t n = 0;    // points in the slice
+    Msm<C> msm;
+};
+
+struct g16_zkey {
+    int device = 0;
+    uint32_t n_vars = 0, n_public = 0, domain_size = 0;
+    int logn = 0;
+    uint64_t n_coefs = 0;
+    int shard_rank = 0, shard_count = 1;
+    HAffine<HFq> alpha1, beta1, delta1;
+    HAffine<HFq2> beta2, delta2;
+    BaseSection<G1> A, B1, C, H;
+    BaseSection<G2> B2;
+    DevBuf row_ptr, col, val;  // CSR of the A rows then the B rows (2n+1 pointers)
+    DevBuf w;                  // witness, n_vars x 32 B standard form
+    DevBuf pa, pb, pc;         // A, B, C evaluations; pa ends up holding the H scalars
+    NttDomain dom;
+    cudaStream_t s_main = nullptr, s_msm[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[16];
+    bool ev_ok = false;
+    bool witness_loaded = false;
+    std::vector<uint8_t> public_bytes;  // w[1..n_public], 32 B each
+    double t_ms[10] = {0};
+    bool partial_done = false;
+
+    ~g16_zkey() {
+        cudaSetDevice(device);
+        if (s_main) cudaStreamDestroy(s_main);
+        for (auto& s : s_msm)
+            if (s) cudaStreamDestroy(s);
+        if (ev_ok)
+            for (auto& e : ev) cudaEventDestroy(e);
+    }
+};
+
+namespace g16 {
+
+static HAffine<HFq> dec_g1(const uint8_t* p) {
+    HAffine<HFq> a;
+    a.x = u256_from_bytes(p);
+    a.y = u256_from_bytes(p + 32);
+    a.inf = u256_is_zero(a.x) && u256_is_zero(a.y);
+    return a;
+}
+static HAffine<HFq2> dec_g2(const uint8_t* p) {
+    HAffine<HFq2> a;
+    a.x.c0 = u256_from_bytes(p);
+    a.x.c1 = u256_from_bytes(p + 32);
+    a.y.c0 = u256_from_bytes(p + 64);
+    a.y.c1 = u256_from_bytes(p + 96);
+    a.inf = HFq2::is_zero(a.x) && HFq2::is_zero(a.y);
+    return a;
+}
+
+static void set_device(int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        throw StatusError(G16_ERR_CUDA, "no CUDA device: libg16b200 has no CPU fallback");
+    if (device >= 0) {
+        if (device >= count) throw StatusError(G16_ERR_CUDA, "CUDA device ordinal out of range");
+        G16_CUDA(cudaSetDevice(device));
+    }
+}
+
+template <class C>
+static void load_section(BaseSection<C>& sec, const Section& s, size_t rec, size_t expect, int rank, int count,
+                         int msm_c, cudaStream_t st, const char* name) {
+    if (s.size != expect * rec) throw FormatError(std::string("zkey: section ") + name + " has the wrong size");
+    sec.lo = expect * size_t(rank) / size_t(count);
+    size_t hi = expect * size_t(rank + 1) / size_t(count);
+    sec.n = hi - sec.lo;
+    sec.bases.alloc(sec.n * rec);
+    sec.mask.alloc(((sec.n + 31) / 32 + 1) * 4);
+    if (sec.n) {
+        G16_CUDA(cudaMemcpyAsync(sec.bases.p, s.p + sec.lo * rec, sec.n * rec, cudaMemcpyHostToDevice, st));
+        msm_inf_mask_kernel<C><<<(unsigned)((sec.n + 255) / 256), 256, 0, st>>>(sec.bases.template as<typename C::aff>(),
+                                                                                (uint32_t)sec.n, sec.mask.template as<uint32_t>());
+        G16_CUDA(cudaGetLastError());
+    }
+    MsmConfig cfg;
+    cfg.c = msm_c;
+    sec.msm.reserve(sec.n ? sec.n : 1, cfg);
+}
+
+static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opts) {
+    g16_opts o;
+    if (opts) o = *opts;
+    else g16_opts_default(&o);
+    set_device(o.device);
+    std::unique_ptr<g16_zkey> zk(new g16_zkey());
+    G16_CUDA(cudaGetDevice(&zk->device));
+    zk->shard_count = o.shard_count > 1 ? o.shard_count : 1;
+    zk->shard_rank = o.shard_count > 1 ? o.shard_rank : 0;
+    if (zk->shard_rank < 0 || zk->shard_rank >= zk->shard_count) throw std::runtime_error("bad shard rank");
+
+    auto secs = parse_binfile(data, len, "zkey", 1);
+    const Section& s1 = need(secs, 1, "zkey");
+    if (s1.size < 4 || rd32(s1.p) != 1) throw FormatError("zkey file is not groth16");
+    const Section& s2 = need(secs, 2, "zkey");
+    const uint8_t* p = s2.p;
+    if (s2.size < 4 + 32 + 4 + 32 + 12 + 64 * 3 + 128 * 3) throw FormatError("zkey: header section too short");
+    uint32_t n8q = rd32(p);
+    if (n8q != 32) throw StatusError(G16_ERR_CURVE, "zkey: curve not supported (n8q != 32)");
+    U256 q = u256_from_bytes(p + 4);
+    uint32_t n8r = rd32(p + 36);
+    if (n8r != 32) throw StatusError(G16_ERR_CURVE, "zkey: curve not supported (n8r != 32)");
+    U256 r = u256_from_bytes(p + 40);
+    if (!u256_eq(q, HFq::mod()) || !u256_eq(r, HFr::mod())) throw StatusError(G16_ERR_CURVE, "zkey: curve is not bn128");
+    p += 72;
+    zk->n_vars = rd32(p);
+    zk->n_public = rd32(p + 4);
+    zk->domain_size = rd32(p + 8);
+    p += 12;
+    uint32_t n = zk->domain_size;
+    if (n < 2 || (n & (n - 1))) throw FormatError("zkey: domain size is not a power of two >= 2");
+    while ((1u << zk->logn) < n) zk->logn++;
+    if (zk->n_public + 1 > zk->n_vars) throw FormatError("zkey: nPublic exceeds nVars");
+    zk->alpha1 = dec_g1(p);
+    zk->beta1 = dec_g1(p + 64);
+    zk->beta2 = dec_g2(p + 128);
+    zk->delta1 = dec_g1(p + 128 + 128 + 128);
+    zk->delta2 = dec_g2(p + 128 + 128 + 128 + 64);
+
+    G16_CUDA(cudaStreamCreateWithFlags(&zk->s_main, cudaStreamNonBlocking));
+    for (auto& s : zk->s_msm) G16_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    for (auto& e : zk->ev) G16_CUDA(cudaEventCreate(&e));
+    zk->ev_ok = true;
+    Msm<G1>::prepare();
+    Msm<G2>::prepare();
+    cudaStream_t st = zk->s_main;
+
+    // sections 5-9: base points (this shard's slice)
+    size_t nv = zk->n_vars;
+    load_section<G1>(zk->A, need(secs, 5, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, st, "5 (A)");
+    load_section<G1>(zk->B1, need(secs, 6, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, st, "6 (B1)");
+    load_section<G2>(zk->B2, need(secs, 7, "zkey"), 128, nv, zk->shard_rank, zk->shard_count, o.msm_c, st, "7 (B2)");
+    load_section<G1>(zk->C, need(secs, 8, "zkey"), 64, nv - zk->n_public - 1, zk->shard_rank, zk->shard_count, o.msm_c,
+                     st, "8 (C)");
+    load_section<G1>(zk->H, need(secs, 9, "zkey"), 64, n, zk->shard_rank, zk->shard_count, o.msm_c, st, "9 (H)");
+
+    // section 4: coefficients -> CSR by (matrix, constraint)
+    const Section& s4 = need(secs, 4, "zkey");
+    if (s4.size < 4) throw FormatError("zkey: coefficient section too short");
+    zk->n_coefs = rd32(s4.p);
+    if (s4.size != 4 + zk->n_coefs * 44) throw FormatError("zkey: coefficient section has the wrong size");
+    {
+        DevBuf raw, counts, bad;
+        raw.alloc(zk->n_coefs * 44);
+        size_t nrows = 2 * size_t(n);
+        counts.alloc((nrows + 1) * 4);
+        bad.alloc(4);
+        zk->row_ptr.alloc((nrows + 1) * 4);
+        zk->col.alloc(zk->n_coefs * 4);
+        zk->val.alloc(zk->n_coefs * 32);
+        G16_CUDA(cudaMemsetAsync(counts.p, 0, (nrows + 1) * 4, st));
+        G16_CUDA(cudaMemsetAsync(bad.p, 0, 4, st));
+        if (zk->n_coefs) {
+            G16_CUDA(cudaMemcpyAsync(raw.p, s4.p + 4, zk->n_coefs * 44, cudaMemcpyHostToDevice, st));
+            unsigned grid = (unsigned)((zk->n_coefs + 255) / 256);
+            r1cs_count_kernel<<<grid, 256, 0, st>>>(raw.as<uint8_t>(), zk->n_coefs, n, zk->n_vars, counts.as<uint32_t>(),
+                                                    bad.as<uint32_t>());
+        }
+        size_t tb = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tb, counts.as<uint32_t>(), zk->row_ptr.as<uint32_t>(), (int)(nrows + 1));
+        DevBuf tmp;
+        tmp.alloc(tb + 16);
+        G16_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, counts.as<uint32_t>(), zk->row_ptr.as<uint32_t>(),
+                                               (int)(nrows + 1), st));
+        G16_CUDA(cudaMemsetAsync(counts.p, 0, (nrows + 1) * 4, st));
+        if (zk->n_coefs) {
+            unsigned grid = (unsigned)((zk->n_coefs + 255) / 256);
+            r1cs_fill_kernel<<<grid, 256, 0, st>>>(raw.as<uint8_t>(), zk->n_coefs, n, zk->row_ptr.as<uint32_t>(),
+                                                   counts.as<uint32_t>(), zk->col.as<uint32_t>(), zk->val.as<fe_t>());
+        }
+        uint32_t hbad = 0;
+        G16_CUDA(cudaMemcpyAsync(&hbad, bad.p, 4, cudaMemcpyDeviceToHost, st));
+        G16_CUDA(cudaStreamSynchronize(st));
+        if (hbad) throw FormatError("zkey: coefficient record out of range (matrix, constraint or signal index)");
+    }
+    zk->w.alloc(size_t(zk->n_vars) * 32);
+    zk->pa.alloc(size_t(n) * 32);
+    zk->pb.alloc(size_t(n) * 32);
+    zk->pc.alloc(size_t(n) * 32);
+    zk->dom.init(zk->logn, st);
+    G16_CUDA(cudaStreamSynchronize(st));
+    return zk.release();
+}
+
+}  // namespace g16
+
+// ---------------------------------------------------------------------------------------------------------
+// output encoding (row a16): the two byte layouts the reference's provers write
+// ---------------------------------------------------------------------------------------------------------
+namespace g16 {
+
+struct J {  // minimal JSON tree: string leaf, list, or ordered object
+    enum Kind { STR, LIST, OBJ } kind = STR;
+    std::string s;
+    std::vector<J> items;
+    std::vector<std::string> keys;
+    static J str(const std::string& v) {
+        J j;
+        j.s = v;
+        return j;
+    }
+    static J list(std::vector<J> v) {
+        J j;
+        j.kind = LIST;
+        j.items = std::move(v);
+        return j;
+    }
+};
+
+// rapidsnark: nlohmann compact dump; snarkjs: JSON.stringify(obj, null, 1); neither ends with a newline
+static void dump(const J& j, int style, int depth, std::string& out) {
+    if (j.kind == J::STR) {
+        out += '"';
+        out += j.s;
+        out += '"';
+        return;
+    }
+    char open = j.kind == J::LIST ? '[' : '{', close = j.kind == J::LIST ? ']' : '}';
+    out += open;
+    if (j.items.empty()) {
+        out += close;
+        return;
+    }
+    for (size_t i = 0; i < j.items.size(); i++) {
+        if (i) out += ',';
+        if (style == G16_STYLE_SNARKJS) {
+            out += '\n';
+            out.append(depth + 1, ' ');
+        }
+        if (j.kind == J::OBJ) {
+            out += '"';
+            out += j.keys[i];
+            out += style == G16_STYLE_SNARKJS ? "\": " : "\":";
+        }
+        dump(j.items[i], style, depth + 1, out);
+    }
+    if (style == G16_STYLE_SNARKJS) {
+        out += '\n';
+        out.append(depth, ' ');
+    }
+    out += close;
+}
+
+static J g1_json(const HAffine<HFq>& a) {
+    if (a.inf) return J::list({J::str("0"), J::str("1"), J::str("0")});
+    return J::list({J::str(u256_to_dec(HFq::from_mont(a.x))), J::str(u256_to_dec(HFq::from_mont(a.y))), J::str("1")});
+}
+static J g2_json(const HAffine<HFq2>& a) {
+    auto pair = [](const std::string& x, const std::string& y) { return J::list({J::str(x), J::str(y)}); };
+    if (a.inf) return J::list({pair("0", "0"), pair("1", "0"), pair("0", "0")});
+    return J::list({pair(u256_to_dec(HFq::from_mont(a.x.c0)), u256_to_dec(HFq::from_mont(a.x.c1))),
+                    pair(u256_to_dec(HFq::from_mont(a.y.c0)), u256_to_dec(HFq::from_mont(a.y.c1))), pair("1", "0")});
+}
+
+static std::string proof_json(const HAffine<HFq>& a, const HAffine<HFq2>& b, const HAffine<HFq>& c, int style) {
+    J o;
+    o.kind = J::OBJ;
+    o.keys = {"pi_a", "pi_b", "pi_c", "protocol"};
+    o.items = {g1_json(a), g2_json(b), g1_json(c), J::str("groth16")};
+    if (style == G16_STYLE_SNARKJS) {
+        o.keys.push_back("curve");
+        o.items.push_back(J::str("bn128"));
+    }
+    std::string out;
+    dump(o, style, 0, out);
+    return out;
+}
+
+static std::string public_json(const std::vector<uint8_t>& pub, int style) {
+    std::vector<J> v;
+    for (size_t i = 0; i + 32 <= pub.size(); i += 32) v.push_back(J::str(u256_to_dec(u256_from_bytes(&pub[i]))));
+    std::string out;
+    dump(J::list(std::move(v)), style, 0, out);
+    return out;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// witness (row a3)
+// ---------------------------------------------------------------------------------------------------------
+static void witness_load(g16_zkey* zk, const uint8_t* data, size_t len) {
+    auto secs = parse_binfile(data, len, "wtns", 2);
+    const Section& s1 = need(secs, 1, "wtns");
+    if (s1.size < 4) throw FormatError("wtns: header section too short");
+    uint32_t n8 = rd32(s1.p);
+    if (s1.size != 4 + uint64_t(n8) + 4) throw FormatError("wtns: header section has the wrong size");
+    if (n8 != 32 || !u256_eq(u256_from_bytes(s1.p + 4), HFr::mod()))
+        throw StatusError(G16_ERR_CURVE, "Curve of the witness does not match the curve of the proving key");
+    uint32_t nw = rd32(s1.p + 4 + n8);
+    if (nw != zk->n_vars)
+        throw StatusError(G16_ERR_WITNESS_LEN, "Invalid witness length. Circuit: " + std::to_string(zk->n_vars) +
+                                                   ", witness: " + std::to_string(nw));
+    const Section& s2 = need(secs, 2, "wtns");
+    if (s2.size != uint64_t(nw) * 32) throw FormatError("wtns: data section has the wrong size");
+    G16_CUDA(cudaSetDevice(zk->device));
+    G16_CUDA(cudaEventRecord(zk->ev[13], zk->s_main));
+    G16_CUDA(cudaMemcpyAsync(zk->w.p, s2.p, size_t(nw) * 32, cudaMemcpyHostToDevice, zk->s_main));
+    G16_CUDA(cudaEventRecord(zk->ev[14], zk->s_main));
+    zk->public_bytes.assign(s2.p + 32, s2.p + 32 + size_t(zk->n_public) * 32);
+    G16_CUDA(cudaStreamSynchronize(zk->s_main));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, zk->ev[13], zk->ev[14]);
+    zk->t_ms[0] = ms;
+    zk->witness_loaded = true;
+    zk->partial_done = false;
+}
+
+// rows a4-a8 on s_main: leaves the H scalars (standard form) in zk->pa
+static void enqueue_h_pipeline(g16_zkey* zk) {
+    cudaStream_t s = zk->s_main;
+    uint32_t n = zk->domain_size;
+    r1cs_eval_kernel<<<(n + 127) / 128, 128, 0, s>>>(zk->row_ptr.as<uint32_t>(), zk->col.as<uint32_t>(),
+                                                     zk->val.as<fe_t>(), zk->w.as<fe_t>(), n, zk->pa.as<fe_t>(),
+                                                     zk->pb.as<fe_t>(), zk->pc.as<fe_t>());
+    G16_CUDA(cudaGetLastError());
+    G16_CUDA(cudaEventRecord(zk->ev[1], s));
+    zk->dom.to_odd_coset(zk->pa.as<fe_t>(), s);
+    zk->dom.to_odd_coset(zk->pb.as<fe_t>(), s);
+    zk->dom.to_odd_coset(zk->pc.as<fe_t>(), s);
+    ntt_join_kernel<<<(n + 255) / 256, 256, 0, s>>>(zk->pa.as<fe_t>(), zk->pb.as<fe_t>(), zk->pc.as<fe_t>(),
+                                                    zk->pa.as<fe_t>(), n);
+    G16_CUDA(cudaGetLastError());
+    G16_CUDA(cudaEventRecord(zk->ev[2], s));
+}
+
+// the device part of a proof: five partial MSM sums of this shard, left in the Msm objects' host buffers
+static void prove_device(g16_zkey* zk) {
+    if (!zk->witness_loaded) throw std::runtime_error("no witness loaded");
+    G16_CUDA(cudaSetDevice(zk->device));
+    auto t0 = std::chrono::steady_clock::now();
+    const uint32_t* w = zk->w.as<uint32_t>();
+    G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
+    // witness-scalar MSMs start at once; the H MSM waits for the NTT pipeline
+    for (int i = 0; i < 4; i++) {
+        G16_CUDA(cudaStreamWaitEvent(zk->s_msm[i], zk->ev[0], 0));
+        G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_msm[i]));
+    }
+    zk->A.msm.stage1(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_msm[0]);
+    zk->B1.msm.stage1(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_msm[1]);
+    zk->B2.msm.stage1(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_msm[2]);
+    zk->C.msm.stage1(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8,
+                     zk->C.mask.as<uint32_t>(), zk->C.n, zk->s_msm[3]);
+    enqueue_h_pipeline(zk);
+    G16_CUDA(cudaStreamWaitEvent(zk->s_msm[4], zk->ev[2], 0));
+    G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_msm[4]));
+    zk->H.msm.stage1(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
+                     zk->s_msm[4]);
+    zk->A.msm.stage2(); zk->B1.msm.stage2(); zk->B2.msm.stage2(); zk->C.msm.stage2(); zk->H.msm.stage2();
+    zk->A.msm.stage3(); zk->B1.msm.stage3(); zk->B2.msm.stage3(); zk->C.msm.stage3(); zk->H.msm.stage3();
+    for (int i = 0; i < 5; i++) G16_CUDA(cudaEventRecord(zk->ev[4 + 2 * i], zk->s_msm[i]));
+    for (int i = 0; i < 5; i++) G16_CUDA(cudaStreamSynchronize(zk->s_msm[i]));
+    G16_CUDA(cudaStreamSynchronize(zk->s_main));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, zk->ev[0], zk->ev[1]); zk->t_ms[1] = ms;
+    cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_ms[2] = ms;
+    for (int i = 0; i < 5; i++) {
+        cudaEventElapsedTime(&ms, zk->ev[3 + 2 * i], zk->ev[4 + 2 * i]);
+        zk->t_ms[3 + i] = ms;
+    }
+    zk->t_ms[8] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    zk->partial_done = true;
+}
+
+static void export_partial(g16_zkey* zk, uint8_t* out) {
+    std::memcpy(out, zk->A.msm.host_result(), 128);
+    std::memcpy(out + 128, zk->B1.msm.host_result(), 128);
+    std::memcpy(out + 256, zk->C.msm.host_result(), 128);
+    std::memcpy(out + 384, zk->H.msm.host_result(), 128);
+    std::memcpy(out + 512, zk->B2.msm.host_result(), 256);
+}
+
+static HPoint<HFq> g1_from_xyzz(const uint8_t* p) {
+    return HPoint<HFq>{u256_from_bytes(p), u256_from_bytes(p + 32), u256_from_bytes(p + 64), u256_from_bytes(p + 96)};
+}
+static HPoint<HFq2> g2_from_xyzz(const uint8_t* p) {
+    HPoint<HFq2> r;
+    r.x = HFq2El{u256_from_bytes(p), u256_from_bytes(p + 32)};
+    r.y = HFq2El{u256_from_bytes(p + 64), u256_from_bytes(p + 96)};
+    r.zz = HFq2El{u256_from_bytes(p + 128), u256_from_bytes(p + 160)};
+    r.zzz = HFq2El{u256_from_bytes(p + 192), u256_from_bytes(p + 224)};
+    return r;
+}
+
+static U256 reduce_scalar(U256 a) {
+    while (u256_cmp(a, HFr::mod()) >= 0) a = HFr::raw_sub(a, HFr::mod());
+    return a;
+}
+static U256 random_scalar() {  // row a14: uniform in Fr by rejection
+    std::random_device rd;
+    for (;;) {
+        U256 a;
+        for (int i = 0; i < 4; i++) a.v[i] = (uint64_t(rd()) << 32) | rd();
+        a.v[3] &= 0x3fffffffffffffffull;
+        if (u256_cmp(a, HFr::mod()) < 0) return a;
+    }
+}
+
+// row a15 + a16
+static void combine(g16_zkey* zk, const uint8_t* partials, int count, const g16_opts& o, std::string& proof,
+                    std::string& pub) {
+    auto t0 = std::chrono::steady_clock::now();
+    HPoint<HFq> a = HG1::identity(), b1 = a, c = a, h = a;
+    HPoint<HFq2> b2 = HG2::identity();
+    for (int i = 0; i < count; i++) {
+        const uint8_t* p = partials + size_t(i) * G16_PARTIAL_BYTES;
+        a = HG1::add(a, g1_from_xyzz(p));
+        b1 = HG1::add(b1, g1_from_xyzz(p + 128));
+        c = HG1::add(c, g1_from_xyzz(p + 256));
+        h = HG1::add(h, g1_from_xyzz(p + 384));
+        b2 = HG2::add(b2, g2_from_xyzz(p + 512));
+    }
+    U256 r, s;
+    if (o.has_rs) {
+        r = reduce_scalar(u256_from_bytes(o.r));
+        s = reduce_scalar(u256_from_bytes(o.s));
+    } else {
+        r = random_scalar();
+        s = random_scalar();
+    }
+    U256 rs = HFr::from_mont(HFr::mul(HFr::to_mont(r), HFr::to_mont(s)));
+    HPoint<HFq> d1 = HG1::from_affine(zk->delta1);
+    HPoint<HFq> pi_a = HG1::add(HG1::add(a, HG1::from_affine(zk->alpha1)), HG1::mul(d1, r));
+    HPoint<HFq2> pi_b = HG2::add(HG2::add(b2, HG2::from_affine(zk->beta2)), HG2::mul(HG2::from_affine(zk->delta2), s));
+    HPoint<HFq> pb1 = HG1::add(HG1::add(b1, HG1::from_affine(zk->beta1)), HG1::mul(d1, s));
+    HPoint<HFq> pi_c = HG1::add(c, h);
+    pi_c = HG1::add(pi_c, HG1::mul(pi_a, s));
+    pi_c = HG1::add(pi_c, HG1::mul(pb1, r));
+    pi_c = HG1::add(pi_c, HG1::neg(HG1::mul(d1, rs)));
+    proof = proof_json(HG1::to_affine(pi_a), HG2::to_affine(pi_b), HG1::to_affine(pi_c), o.style);
+    pub = public_json(zk->public_bytes, o.style);
+    zk->t_ms[9] = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
+
+static int emit(const std::string& proof, const std::string& pub, char* proof_json, size_t* proof_len,
+                char* public_json, size_t* public_len) {
+    if (!proof_len || !public_len) return fail(G16_ERR_GENERIC, "null length pointer");
+    bool shortbuf = *proof_len < proof.size() || *public_len < pub.size() || !proof_json || !public_json;
+    if (!shortbuf) {
+        std::memcpy(proof_json, proof.data(), proof.size());
+        std::memcpy(public_json, pub.data(), pub.size());
+        if (*proof_len > proof.size()) proof_json[proof.size()] = 0;
+        if (*public_len > pub.size()) public_json[pub.size()] = 0;
+    }
+    *proof_len = proof.size();
+    *public_len = pub.size();
+    return shortbuf ? fail(G16_ERR_SHORT_BUFFER, "output buffer too short") : G16_OK;
+}
+
+template <class F>
+static int guarded(F&& f) {
+    try {
+        return f();
+    } catch (const StatusError& e) {
+        return fail(e.code, e.what());
+    } catch (const FormatError& e) {
+        return fail(G16_ERR_FORMAT, e.what());
+    } catch (const std::exception& e) {
+        std::string m = e.what();
+        return fail(m.rfind("CUDA error", 0) == 0 ? G16_ERR_CUDA : G16_ERR_GENERIC, m);
+    }
+}
+
+struct MappedFile {
+    const uint8_t* p = nullptr;
+    size_t len = 0;
+    int fd = -1;
+    explicit MappedFile(const char* path) {
+        fd = ::open(path, O_RDONLY);
+        if (fd < 0) throw std::runtime_error(std::string("cannot open ") + path);
+        struct stat st;
+        if (fstat(fd, &st) != 0) throw std::runtime_error(std::string("cannot stat ") + path);
+        len = (size_t)st.st_size;
+        if (len) {
+            void* m = mmap(nullptr, len, PROT_READ, MAP_PRIVATE, fd, 0);
+            if (m == MAP_FAILED) throw std::runtime_error(std::string("cannot map ") + path);
+            p = static_cast<const uint8_t*>(m);
+        }
+    }
+    ~MappedFile() {
+        if (p) munmap(const_cast<uint8_t*>(p), len);
+        if (fd >= 0) ::close(fd);
+    }
+};
+
+static void write_file(const char* path, const std::string& text) {
+    FILE* f = std::fopen(path, "wb");
+    if (!f) throw std::runtime_error(std::string("cannot write ") + path);
+    size_t w = std::fwrite(text.data(), 1, text.size(), f);
+    if (std::fclose(f) != 0 || w != text.size()) throw std::runtime_error(std::string("short write to ") + path);
+}
+
+}  // namespace g16
+
+// ---------------------------------------------------------------------------------------------------------
+// C ABI
+// ---------------------------------------------------------------------------------------------------------
+extern "C" {
+
+void g16_opts_default(g16_opts* o) {
+    if (!o) return;
+    std::memset(o, 0, sizeof(*o));
+    o->device = -1;
+    o->style = G16_STYLE_RAPIDSNARK;
+    o->shard_count = 1;
+}
+
+const char* g16_last_error(void) { return g_last_error.c_str(); }
+const char* g16_version(void) { return "g16b200 0.1 (sm_100a)"; }
+
+int g16_zkey_open_mem(const uint8_t* data, size_t len, const g16_opts* opts, g16_zkey** out) {
+    return guarded([&]() {
+        if (!data || !out) return fail(G16_ERR_GENERIC, "null argument");
+        *out = zkey_build(data, len, opts);
+        return (int)G16_OK;
+    });
+}
+
+int g16_zkey_open(const char* path, const g16_opts* opts, g16_zkey** out) {
+    return guarded([&]() {
+        if (!path || !out) return fail(G16_ERR_GENERIC, "null argument");
+        MappedFile f(path);
+        *out = zkey_build(f.p, f.len, opts);
+        return (int)G16_OK;
+    });
+}
+
+void g16_zkey_close(g16_zkey* zk) { delete zk; }
+
+int g16_zkey_info(const g16_zkey* zk, uint32_t* n_vars, uint32_t* n_public, uint32_t* domain_size, uint64_t* n_coefs) {
+    if (!zk) return fail(G16_ERR_GENERIC, "null handle");
+    if (n_vars) *n_vars = zk->n_vars;
+    if (n_public) *n_public = zk->n_public;
+    if (domain_size) *domain_size = zk->domain_size;
+    if (n_coefs) *n_coefs = zk->n_coefs;
+    return G16_OK;
+}
+
+int g16_witness_load(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len) {
+    return guarded([&]() {
+        if (!zk || !wtns) return fail(G16_ERR_GENERIC, "null argument");
+        witness_load(zk, wtns, wtns_len);
+        return (int)G16_OK;
+    });
+}
+
+int g16_prove_partial(g16_zkey* zk, uint8_t* partial_out) {
+    return guarded([&]() {
+        if (!zk || !partial_out) return fail(G16_ERR_GENERIC, "null argument");
+        prove_device(zk);
+        export_partial(zk, partial_out);
+        return (int)G16_OK;
+    });
+}
+
+int g16_prove_combine(g16_zkey* zk, const uint8_t* partials, int count, char* proof_json, size_t* proof_len,
+                      char* public_json, size_t* public_len, const g16_opts* opts) {
+    return guarded([&]() {
+        if (!zk || !partials || count < 1) return fail(G16_ERR_GENERIC, "bad argument");
+        g16_opts o;
+        if (opts) o = *opts;
+        else g16_opts_default(&o);
+        std::string proof, pub;
+        combine(zk, partials, count, o, proof, pub);
+        return emit(proof, pub, proof_json, proof_len, public_json, public_len);
+    });
+}
+
+int g16_prove_loaded(g16_zkey* zk, char* proof_json, size_t* proof_len, char* public_json, size_t* public_len,
+                     const g16_opts* opts) {
+    return guarded([&]() {
+        if (!zk) return fail(G16_ERR_GENERIC, "null handle");
+        if (zk->shard_count != 1)
+            return fail(G16_ERR_GENERIC, "handle holds a shard: use g16_prove_partial + g16_prove_combine");
+        g16_opts o;
+        if (opts) o = *opts;
+        else g16_opts_default(&o);
+        uint8_t partial[G16_PARTIAL_BYTES];
+        prove_device(zk);
+        export_partial(zk, partial);
+        std::string proof, pub;
+        combine(zk, partial, 1, o, proof, pub);
+        return emit(proof, pub, proof_json, proof_len, public_json, public_len);
+    });
+}
+
+int g16_prove(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len, char* proof_json, size_t* proof_len,
+              char* public_json, size_t* public_len, const g16_opts* opts) {
+    int rc = g16_witness_load(zk, wtns, wtns_len);
+    if (rc != G16_OK) return rc;
+    return g16_prove_loaded(zk, proof_json, proof_len, public_json, public_len, opts);
+}
+
+int g16_prove_files(const char* zkey_path, const char* wtns_path, const char* proof_path, const char* public_path,
+                    const g16_opts* opts) {
+    return guarded([&]() {
+        if (!zkey_path || !wtns_path || !proof_path || !public_path) return fail(G16_ERR_GENERIC, "null argument");
+        g16_opts o;
+        if (opts) o = *opts;
+        else g16_opts_default(&o);
+        o.shard_count = 1;
+        MappedFile fz(zkey_path), fw(wtns_path);
+        std::unique_ptr<g16_zkey> zk(zkey_build(fz.p, fz.len, &o));
+        witness_load(zk.get(), fw.p, fw.len);
+        uint8_t partial[G16_PARTIAL_BYTES];
+        prove_device(zk.get());
+        export_partial(zk.get(), partial);
+        std::string proof, pub;
+        combine(zk.get(), partial, 1, o, proof, pub);
+        write_file(proof_path, proof);
+        write_file(public_path, pub);
+        return (int)G16_OK;
+    });
+}
+
+int g16_h_scalars(g16_zkey* zk, uint8_t* out) {
+    return guarded([&]() {
+        if (!zk || !out) return fail(G16_ERR_GENERIC, "null argument");
+        if (!zk->witness_loaded) return fail(G16_ERR_GENERIC, "no witness loaded");
+        G16_CUDA(cudaSetDevice(zk->device));
+        enqueue_h_pipeline(zk);
+        G16_CUDA(cudaMemcpyAsync(out, zk->pa.p, size_t(zk->domain_size) * 32, cudaMemcpyDeviceToHost, zk->s_main));
+        G16_CUDA(cudaStreamSynchronize(zk->s_main));
+        return (int)G16_OK;
+    });
+}
+
+int g16_last_timings(const g16_zkey* zk, double out_ms[10]) {
+    if (!zk || !out_ms) return fail(G16_ERR_GENERIC, "null argument");
+    for (int i = 0; i < 10; i++) out_ms[i] = zk->t_ms[i];
+    return G16_OK;
+}
+
+int g16_last_msm_stats(const g16_zkey* zk, uint64_t out[25]) {
+    if (!zk || !out) return fail(G16_ERR_GENERIC, "null argument");
+    const MsmStats* st[5] = {&zk->A.msm.stats, &zk->B1.msm.stats, &zk->B2.msm.stats, &zk->C.msm.stats, &zk->H.msm.stats};
+    for (int i = 0; i < 5; i++) {
+        out[5 * i + 0] = st[i]->entries;
+        out[5 * i + 1] = st[i]->tasks;
+        out[5 * i + 2] = st[i]->cut_buckets;
+        out[5 * i + 3] = (uint64_t)st[i]->c;
+        out[5 * i + 4] = (uint64_t)st[i]->W;
+    }
+    return G16_OK;
+}
+
+}  // extern "C"
