@@ -99,6 +99,8 @@ int g16_msm_stats(const g16_msm* m, uint64_t out[6]);
 /* H-polynomial pipeline on its own (rows a4-a8): witness already loaded; out = domain_size x 32 B standard form
  * (the scalars of the H MSM), host buffer. */
 int g16_h_scalars(g16_zkey* zk, uint8_t* out);
+/* same pipeline, result left on the device (measurement helper: no device->host copy in the call) */
+int g16_h_pipeline_dev(g16_zkey* zk);
 /* odd-coset transform of `count` device-resident vectors of 2^logn Montgomery Fr elements, in place:
  * iNTT, multiply by inc^i, NTT (rows a5-a7).  d_data: count x 2^logn x 32 B. */
 int g16_coset_ntt_dev(void* d_data, int logn, int count);

@@ -1,0 +1,180 @@
+/* Jacobian short-Weierstrass (a = 0) group law over a field given by macros; included twice (Fq -> G1, Fq2 -> G2).
+ * ORACLE CODE - test infrastructure.  Restates wasmcurves 0.2.2 build_curve_jacobian_a0.
+ * Required macros: FE (element type), FN(name) (field function prefix), CN(name) (curve symbol prefix). */
+
+typedef struct { FE x, y; int inf; } CN(aff);
+typedef struct { FE x, y, z; } CN(jac); /* z == 0 -> identity */
+
+static inline void CN(set_inf)(CN(jac) * p) { memset(p, 0, sizeof(*p)); }
+static inline int CN(is_inf)(const CN(jac) * p) { return FN(is_zero)(&p->z); }
+
+static void CN(dbl)(CN(jac) * r, const CN(jac) * p) {
+    if (CN(is_inf)(p)) { *r = *p; return; }
+    FE a, b, c, d, e, f, t;
+    FN(sqr)(&a, &p->x);
+    FN(sqr)(&b, &p->y);
+    FN(sqr)(&c, &b);
+    FN(add)(&t, &p->x, &b); FN(sqr)(&t, &t); FN(sub)(&t, &t, &a); FN(sub)(&t, &t, &c); FN(add)(&d, &t, &t);
+    FN(add)(&e, &a, &a); FN(add)(&e, &e, &a);
+    FN(sqr)(&f, &e);
+    FE x3, y3, z3;
+    FN(sub)(&x3, &f, &d); FN(sub)(&x3, &x3, &d);
+    FN(mul)(&z3, &p->y, &p->z); FN(add)(&z3, &z3, &z3);
+    FN(sub)(&t, &d, &x3); FN(mul)(&y3, &e, &t);
+    FN(add)(&c, &c, &c); FN(add)(&c, &c, &c); FN(add)(&c, &c, &c);
+    FN(sub)(&y3, &y3, &c);
+    r->x = x3; r->y = y3; r->z = z3;
+}
+
+/* r = p + q (q affine, not infinity) */
+static void CN(madd)(CN(jac) * r, const CN(jac) * p, const FE* qx, const FE* qy) {
+    if (CN(is_inf)(p)) { r->x = *qx; r->y = *qy; FN(one)(&r->z); return; }
+    FE z1z1, u2, s2, h, hh, i, j, rr, v, t;
+    FN(sqr)(&z1z1, &p->z);
+    FN(mul)(&u2, qx, &z1z1);
+    FN(mul)(&s2, qy, &p->z); FN(mul)(&s2, &s2, &z1z1);
+    FN(sub)(&h, &u2, &p->x);
+    FN(sub)(&rr, &s2, &p->y);
+    if (FN(is_zero)(&h)) {
+        if (FN(is_zero)(&rr)) { CN(jac) q; q.x = *qx; q.y = *qy; FN(one)(&q.z); CN(dbl)(r, &q); }
+        else CN(set_inf)(r);
+        return;
+    }
+    FN(sqr)(&hh, &h);
+    FN(add)(&i, &hh, &hh); FN(add)(&i, &i, &i);
+    FN(mul)(&j, &h, &i);
+    FN(add)(&rr, &rr, &rr);
+    FN(mul)(&v, &p->x, &i);
+    FE x3, y3, z3;
+    FN(sqr)(&x3, &rr); FN(sub)(&x3, &x3, &j); FN(sub)(&x3, &x3, &v); FN(sub)(&x3, &x3, &v);
+    FN(sub)(&t, &v, &x3); FN(mul)(&y3, &rr, &t);
+    FN(mul)(&t, &p->y, &j); FN(add)(&t, &t, &t); FN(sub)(&y3, &y3, &t);
+    FN(add)(&z3, &p->z, &h); FN(sqr)(&z3, &z3); FN(sub)(&z3, &z3, &z1z1); FN(sub)(&z3, &z3, &hh);
+    r->x = x3; r->y = y3; r->z = z3;
+}
+
+static void CN(add)(CN(jac) * r, const CN(jac) * p, const CN(jac) * q) {
+    if (CN(is_inf)(q)) { *r = *p; return; }
+    if (CN(is_inf)(p)) { *r = *q; return; }
+    FE z1z1, z2z2, u1, u2, s1, s2, h, i, j, rr, v, t;
+    FN(sqr)(&z1z1, &p->z);
+    FN(sqr)(&z2z2, &q->z);
+    FN(mul)(&u1, &p->x, &z2z2);
+    FN(mul)(&u2, &q->x, &z1z1);
+    FN(mul)(&s1, &p->y, &q->z); FN(mul)(&s1, &s1, &z2z2);
+    FN(mul)(&s2, &q->y, &p->z); FN(mul)(&s2, &s2, &z1z1);
+    FN(sub)(&h, &u2, &u1);
+    FN(sub)(&rr, &s2, &s1);
+    if (FN(is_zero)(&h)) {
+        if (FN(is_zero)(&rr)) CN(dbl)(r, p);
+        else CN(set_inf)(r);
+        return;
+    }
+    FN(add)(&i, &h, &h); FN(sqr)(&i, &i);
+    FN(mul)(&j, &h, &i);
+    FN(add)(&rr, &rr, &rr);
+    FN(mul)(&v, &u1, &i);
+    FE x3, y3, z3;
+    FN(sqr)(&x3, &rr); FN(sub)(&x3, &x3, &j); FN(sub)(&x3, &x3, &v); FN(sub)(&x3, &x3, &v);
+    FN(sub)(&t, &v, &x3); FN(mul)(&y3, &rr, &t);
+    FN(mul)(&t, &s1, &j); FN(add)(&t, &t, &t); FN(sub)(&y3, &y3, &t);
+    FN(add)(&z3, &p->z, &q->z); FN(sqr)(&z3, &z3); FN(sub)(&z3, &z3, &z1z1); FN(sub)(&z3, &z3, &z2z2);
+    FN(mul)(&z3, &z3, &h);
+    r->x = x3; r->y = y3; r->z = z3;
+}
+
+static void CN(neg)(CN(jac) * r, const CN(jac) * p) { *r = *p; FN(neg)(&r->y, &p->y); }
+
+static void CN(to_affine)(CN(aff) * r, const CN(jac) * p) {
+    if (CN(is_inf)(p)) { memset(r, 0, sizeof(*r)); r->inf = 1; return; }
+    FE zi, zi2, zi3;
+    FN(inv)(&zi, &p->z);
+    FN(sqr)(&zi2, &zi);
+    FN(mul)(&zi3, &zi2, &zi);
+    FN(mul)(&r->x, &p->x, &zi2);
+    FN(mul)(&r->y, &p->y, &zi3);
+    r->inf = 0;
+}
+
+static void CN(from_affine)(CN(jac) * r, const CN(aff) * a) {
+    if (a->inf) { CN(set_inf)(r); return; }
+    r->x = a->x; r->y = a->y; FN(one)(&r->z);
+}
+
+/* k * p, k = 4 little-endian 64-bit limbs (standard form) */
+static void CN(mul_scalar)(CN(jac) * r, const CN(jac) * p, const uint64_t k[4]) {
+    CN(jac) acc;
+    CN(set_inf)(&acc);
+    for (int i = 255; i >= 0; i--) {
+        CN(dbl)(&acc, &acc);
+        if ((k[i >> 6] >> (i & 63)) & 1) CN(add)(&acc, &acc, p);
+    }
+    *r = acc;
+}
+
+static inline uint32_t CN(window)(const uint64_t* s, int bit, int c) {
+    int limb = bit >> 6, sh = bit & 63;
+    if (limb >= 4) return 0;
+    uint64_t v = s[limb] >> sh;
+    if (sh + c > 64 && limb + 1 < 4) v |= s[limb + 1] << (64 - sh);
+    return (uint32_t)(v & ((1u << c) - 1));
+}
+
+/* Pippenger over one contiguous chunk, single thread (rapidsnark multiexp.cpp / ffjavascript engine_multiexp.js
+ * compute the same sum with their own chunking; the sum does not depend on it).  bases: records of REC bytes
+ * (affine, Montgomery, all-zero = infinity); scalars: 32 B LE standard form. */
+static void CN(pippenger)(CN(jac) * out, const uint8_t* bases, const uint8_t* scalars, size_t n) {
+    CN(set_inf)(out);
+    if (n == 0) return;
+    int c = 1;
+    {
+        double best = 1e300;
+        for (int k = 1; k <= 18; k++) {
+            double cost = ((double)n + 2.0 * (double)(1u << k)) * (double)((254 + k - 1) / k);
+            if (cost < best) { best = cost; c = k; }
+        }
+    }
+    int W = (254 + c - 1) / c;
+    size_t nb = (size_t)1 << c;
+    CN(jac)* bucket = (CN(jac)*)malloc(nb * sizeof(CN(jac)));
+    CN(jac) total;
+    CN(set_inf)(&total);
+    for (int w = W - 1; w >= 0; w--) {
+        for (int i = 0; i < c; i++) CN(dbl)(&total, &total);
+        memset(bucket, 0, nb * sizeof(CN(jac)));
+        for (size_t i = 0; i < n; i++) {
+            uint64_t s[4];
+            memcpy(s, scalars + 32 * i, 32);
+            uint32_t d = CN(window)(s, w * c, c);
+            if (!d) continue;
+            const FE* q = (const FE*)(bases + (size_t)sizeof(FE) * 2 * i);
+            if (FN(is_zero)(&q[0]) && FN(is_zero)(&q[1])) continue;
+            CN(madd)(&bucket[d], &bucket[d], &q[0], &q[1]);
+        }
+        CN(jac) run, acc;
+        CN(set_inf)(&run);
+        CN(set_inf)(&acc);
+        for (size_t b = nb - 1; b >= 1; b--) {
+            CN(add)(&run, &run, &bucket[b]);
+            CN(add)(&acc, &acc, &run);
+        }
+        CN(add)(&total, &total, &acc);
+    }
+    free(bucket);
+    *out = total;
+}
+
+/* all cores: one Pippenger per thread over a contiguous slice, then the partial sums are added */
+static void CN(msm)(CN(jac) * out, const uint8_t* bases, const uint8_t* scalars, size_t n) {
+    int T = omp_get_max_threads();
+    if ((size_t)T > n / 256 + 1) T = (int)(n / 256 + 1);
+    CN(jac)* part = (CN(jac)*)malloc((size_t)T * sizeof(CN(jac)));
+#pragma omp parallel for schedule(static, 1) num_threads(T)
+    for (int t = 0; t < T; t++) {
+        size_t lo = n * (size_t)t / (size_t)T, hi = n * (size_t)(t + 1) / (size_t)T;
+        CN(pippenger)(&part[t], bases + lo * 2 * sizeof(FE), scalars + lo * 32, hi - lo);
+    }
+    CN(set_inf)(out);
+    for (int t = 0; t < T; t++) CN(add)(out, out, &part[t]);
+    free(part);
+}

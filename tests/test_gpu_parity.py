@@ -1,0 +1,354 @@
+"""Parity of the CUDA path against the oracle, through the C ABI (bit-exact: all integer work)."""
+import json
+import os
+import random
+import subprocess
+
+import pytest
+
+from conftest import ROOT
+from oracle import binfile, bn254 as bn, factory, groth16 as g16, verify as V
+
+pytestmark = pytest.mark.gpu
+
+Q, R = bn.Q, bn.R
+MQ, MR = bn.MONT_R_Q, bn.MONT_R_R
+
+
+def le(x):
+    return int(x).to_bytes(32, "little")
+
+
+def ints(b):
+    return [int.from_bytes(b[i:i + 32], "little") for i in range(0, len(b), 32)]
+
+
+EDGE = lambda p: [0, 1, 2, p - 1, p - 2, (1 << 256) % p, (1 << 255) % p, (p + 1) // 2, 0xFFFFFFFF, 1 << 32, (1 << 64) - 1,
+                  (1 << 224) - 1]
+
+
+# ---- field (row a17) ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("field,p", [(0, Q), (1, R)])
+def test_field_ops(pkg, field, p):
+    rng = random.Random(1234 + field)
+    e = EDGE(p)
+    a = [x for x in e for _ in e] + [rng.randrange(p) for _ in range(4000)]
+    b = [y for _ in e for y in e] + [rng.randrange(p) for _ in range(4000)]
+    A, B = b"".join(map(le, a)), b"".join(map(le, b))
+    rinv = bn.inv_mod(1 << 256, p)
+    assert ints(pkg.field_op(field, 0, A, B)) == [x * y * rinv % p for x, y in zip(a, b)]
+    assert ints(pkg.field_op(field, 1, A, B)) == [(x + y) % p for x, y in zip(a, b)]
+    assert ints(pkg.field_op(field, 2, A, B)) == [(x - y) % p for x, y in zip(a, b)]
+    assert ints(pkg.field_op(field, 3, A)) == [(x << 256) % p for x in a]
+    assert ints(pkg.field_op(field, 4, A)) == [x * rinv % p for x in a]
+    sub = a[:200]
+    got = ints(pkg.field_op(field, 5, b"".join(map(le, sub))))
+    # Montgomery inverse: inv(aR) = a^-1 R, i.e. got * x == R^2
+    assert all((g * x - (1 << 512)) % p == 0 if x else g == 0 for g, x in zip(got, sub))
+
+
+def test_field_mul_accepts_unreduced_second_operand(pkg):
+    """The witness is multiplied raw (row a4): b may be any 256-bit value."""
+    rng = random.Random(5)
+    a = [rng.randrange(R) for _ in range(500)]
+    b = [rng.randrange(1 << 256) for _ in range(496)] + [(1 << 256) - 1, R, R + 1, 2 * R]
+    rinv = bn.inv_mod(1 << 256, R)
+    got = ints(pkg.field_op(1, 0, b"".join(map(le, a)), b"".join(map(le, b))))
+    assert got == [x * y * rinv % R for x, y in zip(a, b)]
+
+
+# ---- curve (row a17) ------------------------------------------------------------------------------------
+def rec_g1(p):
+    return binfile.enc_g1(p)
+
+
+def rec_g2(p):
+    return binfile.enc_g2(p)
+
+
+def test_g1_group_law(pkg):
+    G = bn.G1
+    ks = [1, 2, 3, 5, 2, R - 1, R - 2, 77, 1, 12345678901234567890]
+    pts = [G.mul(bn.G1_GEN, k) for k in ks]
+    raw = b"".join(rec_g1(p) for p in pts)
+    want = G.mul(bn.G1_GEN, sum(ks) % R)
+    assert binfile.dec_g1(pkg.curve_op(False, 0, raw, len(pts))) == want
+    assert binfile.dec_g1(pkg.curve_op(False, 1, raw, len(pts))) == want
+    out = pkg.curve_op(False, 2, raw, len(pts))
+    assert [binfile.dec_g1(out[64 * i:64 * i + 64]) for i in range(len(pts))] == [G.mul(p, 2) for p in pts]
+    # P + (-P) = identity, identity records are skipped, P + P through the mixed-add doubling branch
+    p = pts[3]
+    raw = rec_g1(p) + rec_g1(G.neg(p)) + rec_g1(None) + rec_g1(pts[4]) + rec_g1(pts[4])
+    assert binfile.dec_g1(pkg.curve_op(False, 0, raw, 5)) == G.mul(bn.G1_GEN, 4)
+    assert binfile.dec_g1(pkg.curve_op(False, 1, raw, 5)) == G.mul(bn.G1_GEN, 4)
+    assert pkg.curve_op(False, 1, rec_g1(p) + rec_g1(G.neg(p)), 2) == bytes(64)
+
+
+def test_g2_group_law(pkg):
+    G = bn.G2
+    ks = [1, 2, 3, 5, 2, R - 1, 77, 31337]
+    pts = [G.mul(bn.G2_GEN, k) for k in ks]
+    raw = b"".join(rec_g2(p) for p in pts)
+    want = G.mul(bn.G2_GEN, sum(ks) % R)
+    assert binfile.dec_g2(pkg.curve_op(True, 0, raw, len(pts))) == want
+    assert binfile.dec_g2(pkg.curve_op(True, 1, raw, len(pts))) == want
+    out = pkg.curve_op(True, 2, raw, len(pts))
+    assert [binfile.dec_g2(out[128 * i:128 * i + 128]) for i in range(len(pts))] == [G.mul(p, 2) for p in pts]
+
+
+def test_fixed_base_generator_matches_oracle(pkg):
+    rng = random.Random(9)
+    ks = [0, 1, 2, R - 1, 255, 256, 1 << 128] + [rng.randrange(R) for _ in range(20)]
+    sc = b"".join(map(le, ks))
+    o1 = pkg.fixed_base(False, sc, len(ks))
+    o2 = pkg.fixed_base(True, sc, len(ks))
+    for i, k in enumerate(ks):
+        assert binfile.dec_g1(o1[64 * i:64 * i + 64]) == bn.G1.mul(bn.G1_GEN, k)
+        assert binfile.dec_g2(o2[128 * i:128 * i + 128]) == bn.G2.mul(bn.G2_GEN, k)
+
+
+# ---- MSM (rows a9-a13) -------------------------------------------------------------------------------------
+def _msm_case(pkg, is_g2, n, seed, scalar_kind="uniform", zero_bases=0.0, msm_c=0):
+    """bases k_i * G from the GPU fixed-base generator (itself checked above) -> expected = (sum k_i s_i) G"""
+    rng = random.Random(seed)
+    ks = [rng.randrange(1, R) for _ in range(n)]
+    for i in range(n):
+        if rng.random() < zero_bases:
+            ks[i] = 0
+    if scalar_kind == "uniform":
+        ss = [rng.randrange(R) for _ in range(n)]
+    elif scalar_kind == "witness":  # mostly bits / small values, like a circom witness
+        ss = [rng.choice([0, 1, 1, 0, rng.randrange(1 << 64), rng.randrange(R), 1, 0, 2, R - 1]) for _ in range(n)]
+    elif scalar_kind == "ones":
+        ss = [1] * n
+    else:
+        ss = [0] * n
+    bases = pkg.fixed_base(is_g2, b"".join(map(le, ks)), n)
+    got = pkg.msm_host(is_g2, bases, b"".join(map(le, ss)), n, msm_c=msm_c)
+    e = sum(k * s for k, s in zip(ks, ss)) % R
+    if is_g2:
+        assert binfile.dec_g2(got) == bn.G2.mul(bn.G2_GEN, e)
+    else:
+        assert binfile.dec_g1(got) == bn.G1.mul(bn.G1_GEN, e)
+
+
+@pytest.mark.parametrize("n", [1, 2, 31, 33, 1000, 5000])
+def test_msm_g1_uniform(pkg, n):
+    _msm_case(pkg, False, n, 100 + n)
+
+
+@pytest.mark.parametrize("kind", ["witness", "ones", "zeros"])
+def test_msm_g1_scalar_distributions(pkg, kind):
+    _msm_case(pkg, False, 3000, 7, scalar_kind=kind, zero_bases=0.3)
+
+
+@pytest.mark.parametrize("c", [4, 7, 11, 13, 16])
+def test_msm_g1_window_sizes(pkg, c):
+    _msm_case(pkg, False, 2000, 40 + c, msm_c=c)
+
+
+def test_msm_g1_large(pkg):
+    _msm_case(pkg, False, 1 << 17, 21, scalar_kind="witness", zero_bases=0.2)
+    _msm_case(pkg, False, (1 << 16) + 123, 22)
+
+
+@pytest.mark.parametrize("n,kind", [(1, "uniform"), (257, "uniform"), (3000, "witness"), (20000, "uniform")])
+def test_msm_g2(pkg, n, kind):
+    _msm_case(pkg, True, n, 300 + n, scalar_kind=kind, zero_bases=0.35)
+
+
+def test_msm_against_oracle_pippenger_inputs(pkg):
+    """same points, oracle's own msm (not the closed form)"""
+    rng = random.Random(77)
+    pts = [bn.G1.mul(bn.G1_GEN, rng.randrange(1, R)) for _ in range(40)] + [None, None]
+    ss = [rng.randrange(R) for _ in range(42)]
+    got = pkg.msm_host(False, b"".join(rec_g1(p) for p in pts), b"".join(map(le, ss)), 42)
+    assert binfile.dec_g1(got) == bn.G1.msm(pts, ss)
+    assert pkg.msm_host(False, b"", b"", 0) == bytes(64)  # empty input -> infinity
+
+
+def test_msm_linearity_at_scale(pkg):
+    """size-independent property at 2^20: MSM(P, s) + MSM(P, t) == MSM(P, s + t)"""
+    import numpy as np
+    n = 1 << 20
+    rng = np.random.default_rng(5)
+    ks = rng.integers(1, 1 << 62, size=n, dtype=np.uint64)
+    kb = np.zeros((n, 4), dtype=np.uint64)
+    kb[:, 0] = ks
+    bases = pkg.fixed_base(False, kb.tobytes(), n)
+    s = np.zeros((n, 4), dtype=np.uint64)
+    t = np.zeros((n, 4), dtype=np.uint64)
+    s[:, :3] = rng.integers(0, 1 << 63, size=(n, 3), dtype=np.uint64)
+    t[:, :3] = rng.integers(0, 1 << 63, size=(n, 3), dtype=np.uint64)
+    u = s + t  # limbs < 2^64, no carries
+    ps = binfile.dec_g1(pkg.msm_host(False, bases, s.tobytes(), n))
+    pt = binfile.dec_g1(pkg.msm_host(False, bases, t.tobytes(), n))
+    pu = binfile.dec_g1(pkg.msm_host(False, bases, u.tobytes(), n))
+    assert bn.G1.add(ps, pt) == pu
+    # closed form: sum k_i u_i
+    e = 0
+    uu = [int(u[:, j].astype(object) @ ks.astype(object)) for j in range(3)]
+    e = (uu[0] + (uu[1] << 64) + (uu[2] << 128)) % R
+    assert pu == bn.G1.mul(bn.G1_GEN, e)
+
+
+# ---- NTT pipeline (rows a5-a8) ---------------------------------------------------------------------------
+@pytest.mark.parametrize("logn", [1, 2, 5, 10, 11, 13])
+def test_coset_ntt_matches_oracle(pkg, logn):
+    n = 1 << logn
+    rng = random.Random(logn)
+    a = [rng.randrange(R) for _ in range(n)]
+    if n >= 4:
+        a[0], a[1], a[2] = 0, 1, R - 1
+    wn = g16.root_of_unity(logn)
+    inc = g16.root_of_unity(logn + 1)
+    coef = g16.intt(a, wn)
+    t = 1
+    for i in range(n):
+        coef[i] = coef[i] * t % R
+        t = t * inc % R
+    want = g16.ntt(coef, wn)
+    got = ints(pkg.coset_ntt_host(b"".join(le(x * MR % R) for x in a), logn))
+    assert got == [x * MR % R for x in want]
+
+
+def test_coset_ntt_polynomial_property_at_scale(pkg):
+    """2^20: evaluations of a low-degree polynomial on the domain -> its evaluations on the odd coset"""
+    import numpy as np
+    logn = 20
+    n = 1 << logn
+    w = g16.root_of_unity(logn)
+    inc = g16.root_of_unity(logn + 1)
+    c = [3, 5, 7, 11]  # f(x) = 3 + 5x + 7x^2 + 11x^3
+    f = lambda x: (c[0] + c[1] * x + c[2] * x * x + c[3] * x * x * x) % R
+    xs = [1] * n
+    for i in range(1, n):
+        xs[i] = xs[i - 1] * w % R
+    data = b"".join(le(f(x) * MR % R) for x in xs)
+    got = ints(pkg.coset_ntt_host(data, logn))
+    for i in [0, 1, 2, 12345, n // 2, n - 1]:
+        assert got[i] == f(inc * xs[i] % R) * MR % R
+
+
+# ---- full prove (rows a1-a16) ------------------------------------------------------------------------------
+def test_prove_bit_exact_vs_oracle(pkg, small_fixture):
+    f = small_fixture
+    r, s = 0xDEADBEEF << 200 | 17, (R - 5)
+    with pkg.ZKey(bytes(f["zkey_bytes"])) as zk:
+        assert (zk.n_vars, zk.n_public, zk.domain_size) == (85, 2, 128)
+        for style, name in ((pkg.STYLE_RAPIDSNARK, "rapidsnark"), (pkg.STYLE_SNARKJS, "snarkjs")):
+            proof, public = zk.prove(bytes(f["wtns_bytes"]), r=r, s=s, style=style)
+            want_proof, want_public = g16.prove(f["zk"], f["w"], r, s, style=name)
+            assert proof == want_proof and public == want_public
+        # H scalars on their own (rows a4-a8)
+        assert ints(zk.h_scalars()) == g16.h_scalars(f["zk"], f["w"])
+        # fresh randomness: must verify, and differ between calls
+        p1, u1 = zk.prove(bytes(f["wtns_bytes"]))
+        p2, _ = zk.prove(bytes(f["wtns_bytes"]))
+        assert p1 != p2
+        assert V.verify(f["vkey"], json.loads(u1), json.loads(p1))
+        assert V.verify(f["vkey"], json.loads(u1), json.loads(p2))
+
+
+def test_prove_tiny_handmade_circuit(pkg):
+    cons = [([(2, 1)], [(2, 1)], [(3, 1)]), ([(3, 1)], [(2, 1)], [(4, 1)]),
+            ([(4, 1), (2, 1), (0, 5)], [(0, 1)], [(1, 1)])]
+    circ = factory.ListCircuit(5, 1, cons, [1, 35, 3, 9, 27])
+    zk, vkey = factory.setup(circ, factory.Trapdoor(77))
+    with pkg.ZKey(binfile.write_zkey(zk)) as h:
+        proof, public = h.prove(binfile.write_wtns(circ.witness()), r=1111, s=2222)
+    assert (proof, public) == g16.prove(zk, circ.witness(), 1111, 2222)
+    assert V.verify(vkey, ["35"], json.loads(proof))
+
+
+def test_prove_sharded_equals_whole(pkg, small_fixture):
+    """Base-range sharding: 3 shards' partial sums combine to the same proof."""
+    f = small_fixture
+    r, s = 123456789, 987654321
+    want = g16.prove(f["zk"], f["w"], r, s)
+    partials = b""
+    handles = [pkg.ZKey(bytes(f["zkey_bytes"]), shard_rank=k, shard_count=3) for k in range(3)]
+    for h in handles:
+        h.load_witness(bytes(f["wtns_bytes"]))
+        partials += h.prove_partial()
+    assert handles[0].combine(partials, r=r, s=s) == want
+    with pytest.raises(pkg.G16Error):
+        handles[1].prove_loaded(r=r, s=s)
+    for h in handles:
+        h.close()
+
+
+def test_error_conventions(pkg, small_fixture):
+    f = small_fixture
+    with pkg.ZKey(bytes(f["zkey_bytes"])) as zk:
+        with pytest.raises(pkg.G16Error) as e:
+            zk.prove(binfile.write_wtns(f["w"][:-1]))
+        assert e.value.code == pkg.G16_ERR_WITNESS_LEN and "Invalid witness length. Circuit: 85, witness: 84" in e.value.message
+        with pytest.raises(pkg.G16Error) as e:
+            zk.prove(binfile.write_wtns(f["w"], prime=Q))
+        assert e.value.code == pkg.G16_ERR_CURVE and "Curve of the witness does not match" in e.value.message
+        with pytest.raises(pkg.G16Error) as e:
+            zk.prove(b"wtnX" + bytes(f["wtns_bytes"])[4:])
+        assert e.value.code == pkg.G16_ERR_FORMAT
+        with pytest.raises(pkg.G16Error) as e:
+            zk.prove(bytes(f["wtns_bytes"])[:-7])
+        assert e.value.code == pkg.G16_ERR_FORMAT
+    with pytest.raises(pkg.G16Error) as e:
+        pkg.ZKey(bytes(f["zkey_bytes"])[:5000])
+    assert e.value.code == pkg.G16_ERR_FORMAT
+    with pytest.raises(pkg.G16Error) as e:
+        pkg.ZKey(bytes(f["wtns_bytes"]))
+    assert e.value.code == pkg.G16_ERR_FORMAT
+
+
+def test_cli_and_js_api_mirror(pkg, small_fixture, tmp_path):
+    f = small_fixture
+    zp, wp = tmp_path / "c_final.zkey", tmp_path / "witness.wtns"
+    zp.write_bytes(bytes(f["zkey_bytes"]))
+    wp.write_bytes(bytes(f["wtns_bytes"]))
+    exe = os.path.join(ROOT, "zk-proof-of-assets_b200", "prover")
+    env = dict(os.environ, G16_R="1111", G16_S="2222")
+    p = subprocess.run([exe, str(zp), str(wp), str(tmp_path / "proof.json"), str(tmp_path / "public.json")], env=env,
+                       capture_output=True, text=True)
+    assert p.returncode == 0, p.stderr
+    want = g16.prove(f["zk"], f["w"], 1111, 2222)
+    assert ((tmp_path / "proof.json").read_text(), (tmp_path / "public.json").read_text()) == want
+    # snarkjs JS API shape
+    proof, signals = pkg.groth16.prove(str(zp), str(wp), r=1111, s=2222)
+    assert proof == g16.proof_object(*g16.prove_points(f["zk"], f["w"], 1111, 2222), style="snarkjs")
+    assert signals == [str(x) for x in f["w"][1:3]]
+    assert V.verify(f["vkey"], signals, proof)
+    # failure = non-zero exit + message (scripts/lib/error_handling.sh:16-41)
+    bad = tmp_path / "bad.wtns"
+    bad.write_bytes(binfile.write_wtns(f["w"][:-2]))
+    p = subprocess.run([exe, str(zp), str(bad), str(tmp_path / "p2.json"), str(tmp_path / "u2.json")], capture_output=True, text=True)
+    assert p.returncode != 0 and "Invalid witness length" in p.stderr
+    assert not (tmp_path / "p2.json").exists()
+
+
+# ---- SYNTH-1 generator twins + closed form at scale -----------------------------------------------------------
+def test_cuda_fixture_generator_matches_python_factory(pkg, small_fixture):
+    f = small_fixture
+    sy = pkg.Synth(85, 2, 100, 0xB2000001, 0xB2000002)
+    zkey, wtns = sy.write()
+    assert bytes(wtns) == f["wtns_bytes"]
+    assert bytes(zkey) == f["zkey_bytes"]
+    assert sy.vkey() == {k: v for k, v in f["vkey"].items()}
+    pa, pb, pc = factory.closed_form_proof(f["circ"], f["w"], f["td"], 5, 6)
+    assert sy.expected(5, 6) == (pa, pb, pc)
+
+
+@pytest.mark.parametrize("n_vars,n_public,n_cons", [(30000, 1, 32000), (200000, 13, 262130)])
+def test_prove_closed_form_at_scale(pkg, n_vars, n_public, n_cons):
+    """Known trapdoor => the proof for pinned r,s is three scalar multiplications, whatever the size."""
+    sy = pkg.Synth(n_vars, n_public, n_cons, 11, 12)
+    zkey, wtns = sy.write()
+    r, s = 0xABCDEF0123456789 << 64, 0x1F2E3D4C5B6A7988 << 128
+    with pkg.ZKey(zkey) as zk:
+        proof, public = zk.prove(wtns, r=r, s=s)
+        pa, pb, pc = sy.expected(r, s)
+        assert json.loads(proof) == g16.proof_object(pa, pb, pc)
+        p2, u2 = zk.prove(wtns)
+        assert V.verify(sy.vkey(), json.loads(u2), json.loads(p2))
+        st = zk.msm_stats()
+        assert st["H"]["additions"] > 0 and st["B2"]["additions"] > 0

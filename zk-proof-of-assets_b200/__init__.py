@@ -1,0 +1,402 @@
+"""g16-b200: host-side mirror of the reference's prover interface over the C ABI of libg16b200.so.
+
+The reference runs `snarkjs groth16 prove <zkey> <wtns> <proof.json> <public.json>` or rapidsnark's
+`prover` with the same four arguments (scripts/g16_prove.sh:246-260) and, from TypeScript,
+`snarkjs.groth16.prove(zkeyFileName, wtnsFileName) -> {proof, publicSignals}`
+(git_modules/circom-ecdsa/scripts/groupsign_cli.ts:114).  node is not in this image, so the
+host side above the C ABI is this Python module (ctypes, no torch types in any signature):
+
+    groth16.prove(zkey_path, wtns_path)            -> (proof dict, publicSignals list)   [snarkjs JS API]
+    prove_files(zkey, wtns, proof_json, public_json)                                     [the CLI contract]
+    ZKey(path).prove(wtns_bytes)                   -> (proof.json text, public.json text) [resident key]
+
+Everything computes on the GPU through libg16b200.so; there is NO CPU fallback: a missing library
+or a missing device raises.  Nothing here imports oracle/.
+
+The directory name contains '-', so import it by path:
+    importlib.util.spec_from_file_location("g16b200", "<repo>/zk-proof-of-assets_b200/__init__.py")
+(tests/conftest.py, bench.py and __graft_entry__.py do exactly that).
+"""
+import ctypes
+import json
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libg16b200.so")
+SYNTH_LIB_PATH = os.path.join(_HERE, "libg16synth.so")
+
+G16_OK, G16_ERR_GENERIC, G16_ERR_SHORT_BUFFER, G16_ERR_WITNESS_LEN, G16_ERR_CURVE, G16_ERR_CUDA, G16_ERR_FORMAT = range(7)
+STYLE_RAPIDSNARK, STYLE_SNARKJS = 0, 1
+PARTIAL_BYTES = 768
+
+# every symbol include/g16_b200.h declares (tests check the built library exports all of them)
+ABI_SYMBOLS = [
+    "g16_opts_default", "g16_last_error", "g16_version", "g16_zkey_open", "g16_zkey_open_mem", "g16_zkey_close",
+    "g16_zkey_info", "g16_prove", "g16_witness_load", "g16_prove_loaded", "g16_prove_files", "g16_prove_partial",
+    "g16_prove_combine", "g16_msm_g1_host", "g16_msm_g2_host", "g16_msm_create", "g16_msm_destroy", "g16_msm_run_dev",
+    "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
+    "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
+]
+SYNTH_SYMBOLS = [
+    "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
+    "g16_synth_vkey", "g16_synth_fixed_base", "g16_synth_last_error",
+]
+
+
+class G16Error(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("g16 error %d: %s" % (code, message))
+        self.code = code
+        self.message = message
+
+
+class Opts(ctypes.Structure):
+    _fields_ = [
+        ("device", ctypes.c_int32), ("style", ctypes.c_int32), ("has_rs", ctypes.c_int32),
+        ("r", ctypes.c_uint8 * 32), ("s", ctypes.c_uint8 * 32), ("msm_c", ctypes.c_int32),
+        ("shard_rank", ctypes.c_int32), ("shard_count", ctypes.c_int32), ("reserved", ctypes.c_int32 * 8),
+    ]
+
+
+_lib = None
+_synth = None
+
+
+def lib():
+    """The CUDA library.  Fails loudly if it has not been built (`make`, or __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("libg16b200.so is not built (run `make` in the repo root); there is no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        L.g16_last_error.restype = ctypes.c_char_p
+        L.g16_version.restype = ctypes.c_char_p
+        L.g16_zkey_close.restype = None
+        L.g16_msm_destroy.restype = None
+        L.g16_opts_default.restype = None
+        for name in ("g16_msm_g1_host", "g16_msm_g2_host"):
+            getattr(L, name).argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_msm_create.argtypes = [ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_msm_destroy.argtypes = [ctypes.c_void_p]
+        L.g16_msm_run_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+        L.g16_msm_stats.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_open.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_open_mem.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_close.argtypes = [ctypes.c_void_p]
+        L.g16_zkey_info.argtypes = [ctypes.c_void_p] * 5
+        L.g16_prove.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p,
+                                ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_witness_load.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+        L.g16_prove_loaded.argtypes = [ctypes.c_void_p] * 6
+        L.g16_prove_files.argtypes = [ctypes.c_char_p] * 4 + [ctypes.c_void_p]
+        L.g16_prove_partial.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_prove_combine.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5
+        L.g16_h_scalars.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_h_pipeline_dev.argtypes = [ctypes.c_void_p]
+        L.g16_coset_ntt_dev.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        L.g16_coset_ntt_host.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.g16_test_field_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_size_t]
+        L.g16_test_curve_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
+        L.g16_last_timings.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_last_msm_stats.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_bench_int_pipe.argtypes = [ctypes.c_int, ctypes.c_void_p]
+        _lib = L
+    return _lib
+
+
+def synth_lib():
+    """The SYNTH-1 fixture generator (bench/test support; include/g16_synth.h)."""
+    global _synth
+    if _synth is None:
+        if not os.path.exists(SYNTH_LIB_PATH):
+            raise ImportError("libg16synth.so is not built (run `make` in the repo root)")
+        S = ctypes.CDLL(SYNTH_LIB_PATH)
+        S.g16_synth_last_error.restype = ctypes.c_char_p
+        S.g16_synth_destroy.restype = None
+        S.g16_synth_destroy.argtypes = [ctypes.c_void_p]
+        S.g16_synth_create.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_void_p]
+        S.g16_synth_sizes.argtypes = [ctypes.c_void_p] * 4
+        S.g16_synth_write.argtypes = [ctypes.c_void_p] * 3
+        S.g16_synth_expected.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
+        S.g16_synth_vkey.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        S.g16_synth_fixed_base.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
+        _synth = S
+    return _synth
+
+
+def _check(rc):
+    if rc != G16_OK:
+        raise G16Error(rc, lib().g16_last_error().decode("utf-8", "replace"))
+
+
+def make_opts(device=-1, style=STYLE_RAPIDSNARK, r=None, s=None, msm_c=0, shard_rank=0, shard_count=1):
+    o = Opts()
+    lib().g16_opts_default(ctypes.byref(o))
+    o.device, o.style, o.msm_c, o.shard_rank, o.shard_count = device, style, msm_c, shard_rank, shard_count
+    if (r is None) != (s is None):
+        raise ValueError("pin both r and s or neither")
+    if r is not None:
+        o.has_rs = 1
+        o.r[:] = list(int(r).to_bytes(32, "little"))
+        o.s[:] = list(int(s).to_bytes(32, "little"))
+    return o
+
+
+def _addr(buf):
+    """address of a bytes / bytearray / numpy array / ctypes buffer, without copying"""
+    if isinstance(buf, bytes):
+        return ctypes.cast(ctypes.c_char_p(buf), ctypes.c_void_p).value
+    if isinstance(buf, (bytearray, memoryview)):
+        return ctypes.addressof((ctypes.c_char * len(buf)).from_buffer(buf))
+    if hasattr(buf, "ctypes"):
+        return buf.ctypes.data
+    return ctypes.addressof(buf)
+
+
+class ZKey:
+    """A proving key parsed once and kept resident on one GPU (g16_zkey_open).  Mirrors the role of the cached
+    zkeys the workflow reuses across batches (scripts/full_workflow.sh:303-348)."""
+
+    def __init__(self, source, device=-1, msm_c=0, shard_rank=0, shard_count=1):
+        self._h = ctypes.c_void_p()
+        self._opts = make_opts(device=device, msm_c=msm_c, shard_rank=shard_rank, shard_count=shard_count)
+        if isinstance(source, (str, os.PathLike)):
+            _check(lib().g16_zkey_open(os.fsencode(source), ctypes.byref(self._opts), ctypes.byref(self._h)))
+        else:
+            _check(lib().g16_zkey_open_mem(_addr(source), len(source), ctypes.byref(self._opts), ctypes.byref(self._h)))
+        nv, npub, dom, nc = ctypes.c_uint32(), ctypes.c_uint32(), ctypes.c_uint32(), ctypes.c_uint64()
+        _check(lib().g16_zkey_info(self._h, ctypes.byref(nv), ctypes.byref(npub), ctypes.byref(dom), ctypes.byref(nc)))
+        self.n_vars, self.n_public, self.domain_size, self.n_coefs = nv.value, npub.value, dom.value, nc.value
+        self._proof = ctypes.create_string_buffer(4096)
+        self._public = ctypes.create_string_buffer(128 + 80 * max(1, self.n_public))
+
+    def close(self):
+        if self._h:
+            lib().g16_zkey_close(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _out(self, fn, *args):
+        pl, ul = ctypes.c_size_t(len(self._proof)), ctypes.c_size_t(len(self._public))
+        _check(fn(*args, self._proof, ctypes.byref(pl), self._public, ctypes.byref(ul)))
+        return self._proof.raw[:pl.value].decode(), self._public.raw[:ul.value].decode()
+
+    def prove(self, wtns, r=None, s=None, style=STYLE_RAPIDSNARK):
+        """wtns = bytes of a .wtns file (host memory) -> (proof.json text, public.json text)."""
+        o = make_opts(style=style, r=r, s=s)
+        pl, ul = ctypes.c_size_t(len(self._proof)), ctypes.c_size_t(len(self._public))
+        _check(lib().g16_prove(self._h, _addr(wtns), len(wtns), self._proof, ctypes.byref(pl), self._public,
+                               ctypes.byref(ul), ctypes.byref(o)))
+        return self._proof.raw[:pl.value].decode(), self._public.raw[:ul.value].decode()
+
+    def load_witness(self, wtns):
+        _check(lib().g16_witness_load(self._h, _addr(wtns), len(wtns)))
+
+    def prove_loaded(self, r=None, s=None, style=STYLE_RAPIDSNARK):
+        o = make_opts(style=style, r=r, s=s)
+        pl, ul = ctypes.c_size_t(len(self._proof)), ctypes.c_size_t(len(self._public))
+        _check(lib().g16_prove_loaded(self._h, self._proof, ctypes.byref(pl), self._public, ctypes.byref(ul), ctypes.byref(o)))
+        return self._proof.raw[:pl.value].decode(), self._public.raw[:ul.value].decode()
+
+    def prove_partial(self):
+        """This shard's five partial MSM sums (768 bytes) -- the unit the multi-GPU gather moves."""
+        out = ctypes.create_string_buffer(PARTIAL_BYTES)
+        _check(lib().g16_prove_partial(self._h, out))
+        return out.raw
+
+    def combine(self, partials, r=None, s=None, style=STYLE_RAPIDSNARK):
+        assert len(partials) % PARTIAL_BYTES == 0
+        o = make_opts(style=style, r=r, s=s)
+        pl, ul = ctypes.c_size_t(len(self._proof)), ctypes.c_size_t(len(self._public))
+        _check(lib().g16_prove_combine(self._h, _addr(partials), len(partials) // PARTIAL_BYTES, self._proof,
+                                       ctypes.byref(pl), self._public, ctypes.byref(ul), ctypes.byref(o)))
+        return self._proof.raw[:pl.value].decode(), self._public.raw[:ul.value].decode()
+
+    def h_scalars(self):
+        out = ctypes.create_string_buffer(self.domain_size * 32)
+        _check(lib().g16_h_scalars(self._h, out))
+        return out.raw
+
+    def h_pipeline_dev(self):
+        """Run rows a4-a8 on the device and wait; the scalars stay on the GPU (measurement helper)."""
+        _check(lib().g16_h_pipeline_dev(self._h))
+
+    def timings(self):
+        t = (ctypes.c_double * 10)()
+        _check(lib().g16_last_timings(self._h, t))
+        keys = ["h2d_witness", "r1cs_eval", "ntt_pipeline", "msm_A", "msm_B1", "msm_B2", "msm_C", "msm_H", "device_region", "host_final"]
+        return dict(zip(keys, list(t)))
+
+    def msm_stats(self):
+        t = (ctypes.c_uint64 * 25)()
+        _check(lib().g16_last_msm_stats(self._h, t))
+        out = {}
+        for i, name in enumerate(["A", "B1", "B2", "C", "H"]):
+            out[name] = dict(zip(["additions", "tasks", "cut_buckets", "c", "W"], list(t[5 * i:5 * i + 5])))
+        return out
+
+
+class groth16:
+    """`snarkjs.groth16` look-alike: prove(zkeyFileName, wtnsFileName) -> (proof, publicSignals)."""
+
+    @staticmethod
+    def prove(zkey_file_name, wtns_file_name, r=None, s=None, device=-1):
+        with ZKey(zkey_file_name, device=device) as zk, open(wtns_file_name, "rb") as f:
+            proof, public = zk.prove(f.read(), r=r, s=s, style=STYLE_SNARKJS)
+        return json.loads(proof), json.loads(public)
+
+
+def prove_files(zkey_path, wtns_path, proof_path, public_path, r=None, s=None, style=STYLE_RAPIDSNARK, device=-1):
+    """The four-argument command line as one call (scripts/g16_prove.sh:246-252)."""
+    o = make_opts(device=device, style=style, r=r, s=s)
+    _check(lib().g16_prove_files(os.fsencode(zkey_path), os.fsencode(wtns_path), os.fsencode(proof_path),
+                                 os.fsencode(public_path), ctypes.byref(o)))
+
+
+# ---- operators on the path --------------------------------------------------------------------------------
+def msm_host(is_g2, bases, scalars, n, msm_c=0):
+    """bases: n zkey records (64 B G1 / 128 B G2, Montgomery affine); scalars: n x 32 B LE standard form.
+    -> affine Montgomery record of the sum (all-zero = infinity)."""
+    out = ctypes.create_string_buffer(128 if is_g2 else 64)
+    o = make_opts(msm_c=msm_c)
+    fn = lib().g16_msm_g2_host if is_g2 else lib().g16_msm_g1_host
+    _check(fn(bytes(bases), bytes(scalars), n, out, ctypes.byref(o)))
+    return out.raw
+
+
+class Msm:
+    """Reusable workspace for device-resident MSMs (g16_msm_create / g16_msm_run_dev)."""
+
+    def __init__(self, is_g2, max_n, msm_c=0, device=-1):
+        self._h = ctypes.c_void_p()
+        self.is_g2 = is_g2
+        o = make_opts(device=device, msm_c=msm_c)
+        _check(lib().g16_msm_create(int(is_g2), max_n, ctypes.byref(o), ctypes.byref(self._h)))
+
+    def run(self, d_bases, d_scalars, n):
+        out = ctypes.create_string_buffer(128 if self.is_g2 else 64)
+        _check(lib().g16_msm_run_dev(self._h, d_bases, d_scalars, n, out))
+        return out.raw
+
+    def stats(self):
+        t = (ctypes.c_uint64 * 6)()
+        _check(lib().g16_msm_stats(self._h, t))
+        return dict(zip(["additions", "tasks", "cut_buckets", "buckets", "c", "W"], list(t)))
+
+    def close(self):
+        if self._h:
+            lib().g16_msm_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def coset_ntt_host(data, logn):
+    """In place on a copy: evaluations on the 2^logn domain -> evaluations on the odd coset (Montgomery Fr)."""
+    buf = ctypes.create_string_buffer(bytes(data), len(data))
+    _check(lib().g16_coset_ntt_host(buf, logn))
+    return buf.raw
+
+
+def coset_ntt_dev(d_ptr, logn, count=1):
+    _check(lib().g16_coset_ntt_dev(d_ptr, logn, count))
+
+
+def field_op(field, op, a, b=None):
+    n = len(a) // 32
+    out = ctypes.create_string_buffer(len(a))
+    _check(lib().g16_test_field_op(field, op, bytes(a), None if b is None else bytes(b), out, n))
+    return out.raw
+
+
+def curve_op(is_g2, op, points, n):
+    rec = 128 if is_g2 else 64
+    out = ctypes.create_string_buffer(rec * (n if op == 2 else 1))
+    _check(lib().g16_test_curve_op(int(is_g2), op, bytes(points), n, out))
+    return out.raw
+
+
+def bench_int_pipe(op):
+    v = ctypes.c_double()
+    _check(lib().g16_bench_int_pipe(op, ctypes.byref(v)))
+    return v.value
+
+
+# ---- SYNTH-1 fixtures (bench/test support) ------------------------------------------------------------------
+class Synth:
+    """Deterministic synthetic circuit + known-trapdoor setup (include/g16_synth.h)."""
+
+    def __init__(self, n_vars, n_public, n_constraints, circuit_seed=1, trapdoor_seed=2):
+        self._h = ctypes.c_void_p()
+        S = synth_lib()
+        if S.g16_synth_create(n_vars, n_public, n_constraints, circuit_seed, trapdoor_seed, ctypes.byref(self._h)):
+            raise RuntimeError(S.g16_synth_last_error().decode())
+        zb, wb, dom = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint32()
+        S.g16_synth_sizes(self._h, ctypes.byref(zb), ctypes.byref(wb), ctypes.byref(dom))
+        self.zkey_bytes, self.wtns_bytes, self.domain_size = zb.value, wb.value, dom.value
+        self.n_vars, self.n_public, self.n_constraints = n_vars, n_public, n_constraints
+
+    def write(self, want_zkey=True, want_wtns=True):
+        """-> (zkey bytearray | None, wtns bytearray | None); the zkey needs the GPU."""
+        S = synth_lib()
+        zk = bytearray(self.zkey_bytes) if want_zkey else None
+        wt = bytearray(self.wtns_bytes) if want_wtns else None
+        if S.g16_synth_write(self._h, _addr(zk) if zk is not None else None, _addr(wt) if wt is not None else None):
+            raise RuntimeError(S.g16_synth_last_error().decode())
+        return zk, wt
+
+    def expected(self, r, s):
+        """closed-form proof for pinned r,s -> (pi_a (x,y), pi_b ((x0,x1),(y0,y1)), pi_c (x,y)) as ints"""
+        out = ctypes.create_string_buffer(256)
+        if synth_lib().g16_synth_expected(self._h, int(r).to_bytes(32, "little"), int(s).to_bytes(32, "little"), out):
+            raise RuntimeError(synth_lib().g16_synth_last_error().decode())
+        v = [int.from_bytes(out.raw[32 * i:32 * i + 32], "little") for i in range(8)]
+        return (v[0], v[1]), ((v[2], v[3]), (v[4], v[5])), (v[6], v[7])
+
+    def vkey(self):
+        """snarkjs-style verification key dict (decimal strings)."""
+        n = 64 + 3 * 128 + (self.n_public + 1) * 64
+        out = ctypes.create_string_buffer(n)
+        if synth_lib().g16_synth_vkey(self._h, out):
+            raise RuntimeError(synth_lib().g16_synth_last_error().decode())
+        v = [str(int.from_bytes(out.raw[32 * i:32 * i + 32], "little")) for i in range(n // 32)]
+
+        def g2(o):
+            return [[v[o], v[o + 1]], [v[o + 2], v[o + 3]], ["1", "0"]]
+
+        ic = [[v[14 + 2 * i], v[15 + 2 * i], "1"] for i in range(self.n_public + 1)]
+        return {"protocol": "groth16", "curve": "bn128", "nPublic": self.n_public, "vk_alpha_1": [v[0], v[1], "1"],
+                "vk_beta_2": g2(2), "vk_gamma_2": g2(6), "vk_delta_2": g2(10), "IC": ic}
+
+    def close(self):
+        if self._h:
+            synth_lib().g16_synth_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def fixed_base(is_g2, scalars, n):
+    out = ctypes.create_string_buffer((128 if is_g2 else 64) * n)
+    if synth_lib().g16_synth_fixed_base(int(is_g2), bytes(scalars), n, out):
+        raise RuntimeError(synth_lib().g16_synth_last_error().decode())
+    return out.raw

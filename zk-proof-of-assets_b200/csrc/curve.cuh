@@ -34,7 +34,7 @@ struct Curve {
     }
 
     // 2*(x, y)  (dbl-2008-s-1 with ZZ = ZZZ = 1)
-    static __device__ __noinline__ pt dbl_affine(const aff& a) {
+    static __device__ __forceinline__ pt dbl_affine(const aff& a) {
         fe u = F::dbl(a.y);
         fe v = F::sqr(u);
         fe w = F::mul(u, v);
@@ -46,7 +46,7 @@ struct Curve {
         return pt{x3, y3, v, w};
     }
 
-    static __device__ __noinline__ pt dbl(const pt& p) {
+    static __device__ __forceinline__ pt dbl(const pt& p) {
         if (is_identity(p)) return p;
         fe u = F::dbl(p.y);
         fe v = F::sqr(u);
@@ -86,7 +86,7 @@ struct Curve {
     }
 
     // acc += b (add-2008-s), all cases
-    static __device__ __noinline__ void add(pt& acc, const pt& b) {
+    static __device__ __forceinline__ void add(pt& acc, const pt& b) {
         if (is_identity(b)) return;
         if (is_identity(acc)) {
             acc = b;

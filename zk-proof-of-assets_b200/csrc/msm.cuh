@@ -184,9 +184,12 @@ msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t*
     else buckets[out] = acc;
 }
 
-// block-wide tree sum of XYZZ points held one per thread; result in thread 0
+// block-wide tree sum of XYZZ points held one per thread; result in every thread.
+// The staging array is STATIC shared memory (16 KB G1 / 32 KB G2 at 128 threads): with an `extern __shared__`
+// byte array cast to pt*, nvcc 12.9 drops the first 16-byte store of `sh[threadIdx.x] = acc` (seen in the PTX).
 template <class C, int THREADS>
-__device__ __forceinline__ void block_sum_points(typename C::pt& acc, typename C::pt* sh) {
+__device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
+    __shared__ typename C::pt sh[THREADS];
     sh[threadIdx.x] = acc;
     __syncthreads();
     for (int s = THREADS / 2; s > 0; s >>= 1) {
@@ -205,13 +208,11 @@ template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 msm_combine_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __restrict__ part_base,
                    const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ buckets) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    typename C::pt* sh = reinterpret_cast<typename C::pt*>(smem_raw);
     uint32_t k = cut_list[blockIdx.x];
     uint32_t b = part_base[k], e = part_base[k + 1];
     typename C::pt acc = C::identity();
     for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts[i]);
-    block_sum_points<C, THREADS>(acc, sh);
+    block_sum_points<C, THREADS>(acc);
     if (threadIdx.x == 0) buckets[k] = acc;
 }
 
@@ -244,12 +245,10 @@ template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 msm_window_sum_kernel(const typename C::pt* __restrict__ chunk_out, uint32_t chunks_per_window,
                       typename C::pt* __restrict__ window_out) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    typename C::pt* sh = reinterpret_cast<typename C::pt*>(smem_raw);
     const typename C::pt* p = chunk_out + size_t(blockIdx.x) * chunks_per_window;
     typename C::pt acc = C::identity();
     for (uint32_t i = threadIdx.x; i < chunks_per_window; i += THREADS) C::add(acc, p[i]);
-    block_sum_points<C, THREADS>(acc, sh);
+    block_sum_points<C, THREADS>(acc);
     if (threadIdx.x == 0) window_out[blockIdx.x] = acc;
 }
 
@@ -432,7 +431,7 @@ public:
                 buckets.as<pt>(), parts.as<pt>());
             G16_CUDA(cudaGetLastError());
             if (ncut) {
-                msm_combine_kernel<C, RED_THREADS><<<ncut, RED_THREADS, RED_THREADS * sizeof(pt), s>>>(
+                msm_combine_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
                     cut_list.as<uint32_t>(), part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
                 G16_CUDA(cudaGetLastError());
             }
@@ -440,7 +439,7 @@ public:
         uint32_t nchunks = uint32_t(W) * cpw;
         msm_chunk_reduce_kernel<C><<<(nchunks + 63) / 64, 64, 0, s>>>(buckets.as<pt>(), bpw, L, cpw, nchunks,
                                                                       chunk_out.as<pt>());
-        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, RED_THREADS * sizeof(pt), s>>>(chunk_out.as<pt>(), cpw,
+        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(chunk_out.as<pt>(), cpw,
                                                                                               window_out.as<pt>());
         msm_horner_kernel<C><<<1, 32, 0, s>>>(window_out.as<pt>(), W, c, result.as<pt>());
         G16_CUDA(cudaGetLastError());
@@ -457,12 +456,7 @@ public:
     }
     const pt* host_result() const { return h_result; }  // valid after the stream is synchronised
     const pt* device_result() const { return result.as<pt>(); }
-    static void prepare() {  // opt in to > 48 KB dynamic shared memory for the G2 reductions
-        cudaFuncSetAttribute(msm_combine_kernel<C, RED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(RED_THREADS * sizeof(pt)));
-        cudaFuncSetAttribute(msm_window_sum_kernel<C, RED_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(RED_THREADS * sizeof(pt)));
-    }
+    static void prepare() {}
 
     MsmStats stats;
     int c = 0, W = 0;

@@ -103,14 +103,12 @@ __global__ void curve_chain_kernel(const typename C::aff* pts, size_t n, typenam
 // op 1: block tree of full additions (128 threads)
 template <class C>
 __global__ void curve_tree_kernel(const typename C::aff* pts, size_t n, typename C::pt* out) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    typename C::pt* sh = reinterpret_cast<typename C::pt*>(smem_raw);
     typename C::pt acc = C::identity();
     for (size_t i = threadIdx.x; i < n; i += 128) {
         typename C::pt p = C::from_affine(pts[i]);
         C::add(acc, p);
     }
-    block_sum_points<C, 128>(acc, sh);
+    block_sum_points<C, 128>(acc);
     if (threadIdx.x == 0) *out = acc;
 }
 // op 2: doubling, one thread per point, through both dbl paths
@@ -143,8 +141,7 @@ int curve_op(int op, const uint8_t* points, size_t n, uint8_t* out, void (*conv)
     G16_CUDA(cudaMemcpy(dp.p, points, n * sizeof(aff), cudaMemcpyHostToDevice));
     if (op == 0) curve_chain_kernel<C><<<1, 32>>>(dp.as<aff>(), n, dout.as<pt>());
     else if (op == 1) {
-        cudaFuncSetAttribute(curve_tree_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(128 * sizeof(pt)));
-        curve_tree_kernel<C><<<1, 128, 128 * sizeof(pt)>>>(dp.as<aff>(), n, dout.as<pt>());
+        curve_tree_kernel<C><<<1, 128>>>(dp.as<aff>(), n, dout.as<pt>());
     } else curve_dbl_kernel<C><<<(unsigned)((n + 63) / 64), 64>>>(dp.as<aff>(), n, dout.as<pt>());
     G16_CUDA(cudaGetLastError());
     std::vector<pt> h(nout);

@@ -781,6 +781,21 @@ int g16_h_scalars(g16_zkey* zk, uint8_t* out) {
     });
 }
 
+int g16_h_pipeline_dev(g16_zkey* zk) {
+    return guarded([&]() {
+        if (!zk) return fail(G16_ERR_GENERIC, "null argument");
+        if (!zk->witness_loaded) return fail(G16_ERR_GENERIC, "no witness loaded");
+        G16_CUDA(cudaSetDevice(zk->device));
+        G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
+        enqueue_h_pipeline(zk);
+        G16_CUDA(cudaStreamSynchronize(zk->s_main));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, zk->ev[0], zk->ev[1]); zk->t_ms[1] = ms;
+        cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_ms[2] = ms;
+        return (int)G16_OK;
+    });
+}
+
 int g16_last_timings(const g16_zkey* zk, double out_ms[10]) {
     if (!zk || !out_ms) return fail(G16_ERR_GENERIC, "null argument");
     for (int i = 0; i < 10; i++) out_ms[i] = zk->t_ms[i];
