@@ -120,6 +120,12 @@ int g16_test_curve_op(int is_g2, int op, const uint8_t* points, size_t n, uint8_
 int g16_last_timings(const g16_zkey* zk, double out_ms[10]);
 /* counters of the last prove: per MSM (A,B1,B2,C,H) x {mixed additions, tasks, cut buckets, c, W} */
 int g16_last_msm_stats(const g16_zkey* zk, uint64_t out[25]);
+/* duration of the bucket-accumulation kernel (the dominant kernel) of each MSM of the last prove, milliseconds,
+ * CUDA events on the stream the kernel ran on: A, B1, B2, C, H */
+int g16_last_accumulate_ms(const g16_zkey* zk, double out[5]);
+/* cumulative number of this library's own kernel launches in this process (library kernels such as cub's are
+ * not counted) */
+unsigned long long g16_launch_count(void);
 /* integer-pipe microbenchmark: op 0 = 32-bit IMAD, 1 = IMAD.WIDE.U32 (+carry chain), 2 = Montgomery products.
  * Returns achieved ops per second over the whole device (op 2: field products per second). */
 int g16_bench_int_pipe(int op, double* ops_per_s);

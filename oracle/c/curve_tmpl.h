@@ -147,7 +147,8 @@ static void CN(pippenger)(CN(jac) * out, const uint8_t* bases, const uint8_t* sc
             memcpy(s, scalars + 32 * i, 32);
             uint32_t d = CN(window)(s, w * c, c);
             if (!d) continue;
-            const FE* q = (const FE*)(bases + (size_t)sizeof(FE) * 2 * i);
+            FE q[2]; /* records sit at arbitrary byte offsets of the file: copy, do not cast */
+            memcpy(q, bases + sizeof(FE) * 2 * i, sizeof(q));
             if (FN(is_zero)(&q[0]) && FN(is_zero)(&q[1])) continue;
             CN(madd)(&bucket[d], &bucket[d], &q[0], &q[1]);
         }
@@ -165,15 +166,20 @@ static void CN(pippenger)(CN(jac) * out, const uint8_t* bases, const uint8_t* sc
 }
 
 /* all cores: one Pippenger per thread over a contiguous slice, then the partial sums are added */
+typedef struct { const uint8_t *bases, *scalars; size_t n; int T; CN(jac) * part; } CN(msm_ctx);
+static void CN(msm_range)(size_t lo, size_t hi, void* p) {
+    CN(msm_ctx)* c = (CN(msm_ctx)*)p;
+    for (size_t t = lo; t < hi; t++) {
+        size_t a = c->n * t / (size_t)c->T, b = c->n * (t + 1) / (size_t)c->T;
+        CN(pippenger)(&c->part[t], c->bases + a * 2 * sizeof(FE), c->scalars + a * 32, b - a);
+    }
+}
 static void CN(msm)(CN(jac) * out, const uint8_t* bases, const uint8_t* scalars, size_t n) {
-    int T = omp_get_max_threads();
+    int T = n_threads();
     if ((size_t)T > n / 256 + 1) T = (int)(n / 256 + 1);
     CN(jac)* part = (CN(jac)*)malloc((size_t)T * sizeof(CN(jac)));
-#pragma omp parallel for schedule(static, 1) num_threads(T)
-    for (int t = 0; t < T; t++) {
-        size_t lo = n * (size_t)t / (size_t)T, hi = n * (size_t)(t + 1) / (size_t)T;
-        CN(pippenger)(&part[t], bases + lo * 2 * sizeof(FE), scalars + lo * 32, hi - lo);
-    }
+    CN(msm_ctx) c = {bases, scalars, n, T, part};
+    par_range((size_t)T, 0, CN(msm_range), &c);
     CN(set_inf)(out);
     for (int t = 0; t < T; t++) CN(add)(out, out, &part[t]);
     free(part);

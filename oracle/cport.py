@@ -1,0 +1,133 @@
+"""ctypes binding of the C oracle (oracle/c/oracle.c).  ORACLE CODE: test infrastructure / timed CPU baseline only."""
+import ctypes
+import os
+import subprocess
+
+from . import bn254 as bn
+from . import groth16 as g16
+
+_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "c")
+_LIB = os.path.join(_DIR, "liboracle.so")
+_lib = None
+
+
+def build(force=False):
+    src = [os.path.join(_DIR, f) for f in ("oracle.c", "curve_tmpl.h", "Makefile")]
+    stale = not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in src)
+    if force or stale:
+        # -march=native is per machine: a library built in the build container may not run on the GPU box's CPU,
+        # so rebuild where it is used if the toolchain is there
+        subprocess.run(["make", "-C", _DIR, "-B", "liboracle.so"], check=True, capture_output=True)
+    return _LIB
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        marker = _LIB + ".host"
+        host = open("/proc/cpuinfo").read().split("flags")[1].split("\n")[0] if os.path.exists("/proc/cpuinfo") else ""
+        tag = str(hash(host))
+        if not os.path.exists(_LIB) or not os.path.exists(marker) or open(marker).read() != tag:
+            build(force=True)
+            with open(marker, "w") as f:
+                f.write(tag)
+        L = ctypes.CDLL(_LIB)
+        L.orc_threads.restype = ctypes.c_int
+        L.orc_set_threads.argtypes = [ctypes.c_int]
+        L.orc_last_timings.argtypes = [ctypes.c_void_p]
+        L.orc_field_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_size_t]
+        L.orc_msm_g1.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+        L.orc_msm_g2.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+        L.orc_coset_ntt.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.orc_h_scalars.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+        L.orc_prove.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p,
+                                ctypes.c_char_p, ctypes.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _addr(buf):
+    if isinstance(buf, bytes):
+        return ctypes.cast(ctypes.c_char_p(buf), ctypes.c_void_p).value
+    if isinstance(buf, (bytearray, memoryview)):
+        return ctypes.addressof((ctypes.c_char * len(buf)).from_buffer(buf))
+    if hasattr(buf, "ctypes"):
+        return buf.ctypes.data
+    return ctypes.addressof(buf)
+
+
+def threads():
+    return lib().orc_threads()
+
+
+def set_threads(n):
+    lib().orc_set_threads(n)
+
+
+def field_op(field, op, a, b=None):
+    out = ctypes.create_string_buffer(len(a))
+    lib().orc_field_op(field, op, bytes(a), None if b is None else bytes(b), out, len(a) // 32)
+    return out.raw
+
+
+def msm(is_g2, bases, scalars, n):
+    out = ctypes.create_string_buffer(128 if is_g2 else 64)
+    (lib().orc_msm_g2 if is_g2 else lib().orc_msm_g1)(_addr(bases), _addr(scalars), n, out)
+    return out.raw
+
+
+def coset_ntt(data, logn):
+    buf = ctypes.create_string_buffer(bytes(data), len(data))
+    lib().orc_coset_ntt(buf, logn)
+    return buf.raw
+
+
+def h_scalars(zkey, wtns):
+    n = int.from_bytes(_section(zkey, 2)[80:84], "little")
+    out = ctypes.create_string_buffer(n * 32)
+    rc = lib().orc_h_scalars(_addr(zkey), len(zkey), _addr(wtns), len(wtns), out)
+    if rc:
+        raise ValueError("orc_h_scalars: code %d" % rc)
+    return out.raw
+
+
+def _section(data, typ):
+    pos = 12
+    nsec = int.from_bytes(data[8:12], "little")
+    for _ in range(nsec):
+        t = int.from_bytes(data[pos:pos + 4], "little")
+        size = int.from_bytes(data[pos + 4:pos + 12], "little")
+        pos += 12
+        if t == typ:
+            return data[pos:pos + size]
+        pos += size
+    raise ValueError("missing section %d" % typ)
+
+
+def prove_points(zkey, wtns, r, s):
+    """-> (pi_a, pi_b, pi_c) affine ints in oracle.bn254 conventions (None = infinity)."""
+    out = ctypes.create_string_buffer(256)
+    rc = lib().orc_prove(_addr(zkey), len(zkey), _addr(wtns), len(wtns), int(r % (1 << 256)).to_bytes(32, "little"),
+                         int(s % (1 << 256)).to_bytes(32, "little"), out)
+    if rc:
+        raise ValueError("orc_prove: code %d" % rc)
+    v = [int.from_bytes(out.raw[32 * i:32 * i + 32], "little") for i in range(8)]
+    pa = None if v[0] == 0 and v[1] == 0 else (v[0], v[1])
+    pb = None if not any(v[2:6]) else ((v[2], v[3]), (v[4], v[5]))
+    pc = None if v[6] == 0 and v[7] == 0 else (v[6], v[7])
+    return pa, pb, pc
+
+
+def prove(zkey, wtns, r, s, style="rapidsnark"):
+    """-> (proof.json text, public.json text), same layout rules as oracle.groth16.prove."""
+    pa, pb, pc = prove_points(zkey, wtns, r, s)
+    npub = int.from_bytes(_section(zkey, 2)[76:80], "little")
+    w = _section(wtns, 2)
+    public = [str(int.from_bytes(w[32 * i:32 * i + 32], "little")) for i in range(1, npub + 1)]
+    return g16.dumps(g16.proof_object(pa, pb, pc, style), style), g16.dumps(public, style)
+
+
+def last_timings():
+    t = (ctypes.c_double * 8)()
+    lib().orc_last_timings(t)
+    return dict(zip(["abc", "ntt_join", "msm_A", "msm_B1", "msm_B2", "msm_C", "msm_H", "total"], list(t)))

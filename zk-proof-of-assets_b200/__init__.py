@@ -36,6 +36,7 @@ ABI_SYMBOLS = [
     "g16_prove_combine", "g16_msm_g1_host", "g16_msm_g2_host", "g16_msm_create", "g16_msm_destroy", "g16_msm_run_dev",
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
+    "g16_last_accumulate_ms", "g16_launch_count",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -100,6 +101,8 @@ def lib():
         L.g16_last_timings.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.g16_last_msm_stats.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.g16_bench_int_pipe.argtypes = [ctypes.c_int, ctypes.c_void_p]
+        L.g16_last_accumulate_ms.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_launch_count.restype = ctypes.c_ulonglong
         _lib = L
     return _lib
 
@@ -150,6 +153,8 @@ def _addr(buf):
         return ctypes.addressof((ctypes.c_char * len(buf)).from_buffer(buf))
     if hasattr(buf, "ctypes"):
         return buf.ctypes.data
+    if hasattr(buf, "data_ptr"):  # a (pinned) host tensor used as a plain buffer
+        return buf.data_ptr()
     return ctypes.addressof(buf)
 
 
@@ -237,6 +242,11 @@ class ZKey:
         _check(lib().g16_last_timings(self._h, t))
         keys = ["h2d_witness", "r1cs_eval", "ntt_pipeline", "msm_A", "msm_B1", "msm_B2", "msm_C", "msm_H", "device_region", "host_final"]
         return dict(zip(keys, list(t)))
+
+    def accumulate_ms(self):
+        t = (ctypes.c_double * 5)()
+        _check(lib().g16_last_accumulate_ms(self._h, t))
+        return dict(zip(["A", "B1", "B2", "C", "H"], list(t)))
 
     def msm_stats(self):
         t = (ctypes.c_uint64 * 25)()
@@ -329,6 +339,10 @@ def curve_op(is_g2, op, points, n):
     out = ctypes.create_string_buffer(rec * (n if op == 2 else 1))
     _check(lib().g16_test_curve_op(int(is_g2), op, bytes(points), n, out))
     return out.raw
+
+
+def launch_count():
+    return int(lib().g16_launch_count())
 
 
 def bench_int_pipe(op):

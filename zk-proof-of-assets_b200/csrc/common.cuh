@@ -1,6 +1,7 @@
 // Shared host-side helpers: CUDA error check and an owning device buffer.
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <stdexcept>
 #include <string>
 
@@ -13,6 +14,13 @@ namespace g16 {
             throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " +    \
                                      __FILE__ + ":" + std::to_string(__LINE__));                        \
     } while (0)
+
+// number of this library's own kernels launched so far (bench.py's gpu_launches; cub's kernels are not counted)
+inline std::atomic<unsigned long long>& launch_counter() {
+    static std::atomic<unsigned long long> c{0};
+    return c;
+}
+#define G16_LAUNCHED(n) (::g16::launch_counter() += (n))
 
 struct DevBuf {
     void* p = nullptr;

@@ -14,9 +14,10 @@
 //   accumulate (the hot kernel, IMAD bound): one thread per task, XYZZ mixed additions, next point prefetched
 //   combine  : buckets that were cut are summed by one CTA each
 //   reduce   : per chunk of L buckets a running-sum gives sum (b+1) B_b; chunks are tree-summed per window
-//   windows  : Horner over the W window sums (c doublings each)
+//   windows  : the W window sums go to the host, which runs the Horner chain (c doublings per window)
 #pragma once
 #include <cub/cub.cuh>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include "common.cuh"
@@ -110,17 +111,32 @@ static __global__ void msm_bounds_kernel(const uint32_t* __restrict__ keys, uint
     if (i == m - 1 || keys[i + 1] != k) end[k] = i + 1;
 }
 
-// per bucket: number of tasks, number of partial-sum slots (0 unless the bucket is cut), list of cut buckets
+// per bucket: number of tasks, number of partial-sum slots (0 unless the bucket is cut), number of first-level
+// combine blocks (COMBINE_GROUP partial sums each), list of cut buckets
+constexpr uint32_t COMBINE_GROUP = 1024;
 static __global__ void msm_count_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end, uint32_t nb,
                                        uint32_t T, uint32_t* __restrict__ ntasks, uint32_t* __restrict__ nparts,
-                                       uint32_t* __restrict__ cut_list, uint32_t* __restrict__ cut_count) {
+                                       uint32_t* __restrict__ nblk, uint32_t* __restrict__ cut_list,
+                                       uint32_t* __restrict__ cut_count) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k > nb) return;
     uint32_t t = 0;
     if (k < nb) t = (end[k] - start[k] + T - 1) / T;
     ntasks[k] = t;
     nparts[k] = t > 1 ? t : 0;
+    nblk[k] = t > 1 ? (t + COMBINE_GROUP - 1) / COMBINE_GROUP : 0;
     if (t > 1) cut_list[atomicAdd(cut_count, 1u)] = k;
+}
+
+// last k with base[k] <= j (base has nb+1 non-decreasing entries, base[nb] = total)
+static __device__ __forceinline__ uint32_t msm_owner(const uint32_t* __restrict__ base, uint32_t nb, uint32_t j) {
+    uint32_t lo = 0, hi = nb;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi + 1) >> 1;
+        if (base[mid] <= j) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
 }
 
 // task j -> (first entry, length, output slot); slot bit 31 set = partial-sum array, else bucket array
@@ -131,14 +147,7 @@ static __global__ void msm_make_tasks_kernel(const uint32_t* __restrict__ start,
                                       uint32_t* __restrict__ sort_key, uint32_t* __restrict__ sort_val) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= nt) return;
-    // last k with task_base[k] <= j  (task_base has nb+1 entries, non-decreasing, task_base[nb] = nt)
-    uint32_t lo = 0, hi = nb;
-    while (lo < hi) {
-        uint32_t mid = (lo + hi + 1) >> 1;
-        if (task_base[mid] <= j) lo = mid;
-        else hi = mid - 1;
-    }
-    uint32_t k = lo;
+    uint32_t k = msm_owner(task_base, nb, j);
     uint32_t local = j - task_base[k];
     uint32_t b = start[k] + local * T;
     uint32_t len = min(T, end[k] - b);
@@ -203,15 +212,31 @@ __device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
     acc = sh[0];
 }
 
-// one CTA per cut bucket: sum its partial sums
+// Cut buckets are summed in two levels so that a bucket holding a quarter of all points (the digit-1 bucket of a
+// circom witness) is still a short dependency chain: level 1 = one CTA per COMBINE_GROUP partial sums,
+// level 2 = one CTA per cut bucket over its level-1 results.
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-msm_combine_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __restrict__ part_base,
-                   const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ buckets) {
-    uint32_t k = cut_list[blockIdx.x];
-    uint32_t b = part_base[k], e = part_base[k + 1];
+msm_combine1_kernel(const uint32_t* __restrict__ blk_base, const uint32_t* __restrict__ part_base, uint32_t nb,
+                    const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ parts2) {
+    uint32_t k = msm_owner(blk_base, nb, blockIdx.x);
+    uint32_t g = blockIdx.x - blk_base[k];
+    uint32_t b = part_base[k] + g * COMBINE_GROUP;
+    uint32_t e = min(part_base[k + 1], b + COMBINE_GROUP);
     typename C::pt acc = C::identity();
     for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts[i]);
+    block_sum_points<C, THREADS>(acc);
+    if (threadIdx.x == 0) parts2[blockIdx.x] = acc;
+}
+
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+msm_combine2_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __restrict__ blk_base,
+                    const typename C::pt* __restrict__ parts2, typename C::pt* __restrict__ buckets) {
+    uint32_t k = cut_list[blockIdx.x];
+    uint32_t b = blk_base[k], e = blk_base[k + 1];
+    typename C::pt acc = C::identity();
+    for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts2[i]);
     block_sum_points<C, THREADS>(acc);
     if (threadIdx.x == 0) buckets[k] = acc;
 }
@@ -252,19 +277,6 @@ msm_window_sum_kernel(const typename C::pt* __restrict__ chunk_out, uint32_t chu
     if (threadIdx.x == 0) window_out[blockIdx.x] = acc;
 }
 
-// Horner over windows: result = sum_w 2^(c w) S_w
-template <class C>
-__global__ void msm_horner_kernel(const typename C::pt* __restrict__ window_out, int W, int c,
-                                  typename C::pt* __restrict__ result) {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    typename C::pt acc = window_out[W - 1];
-    for (int w = W - 2; w >= 0; w--) {
-        for (int i = 0; i < c; i++) acc = C::dbl(acc);
-        C::add(acc, window_out[w]);
-    }
-    *result = acc;
-}
-
 // bit i of mask = base i is the all-zero record (infinity)
 template <class C>
 __global__ void msm_inf_mask_kernel(const typename C::aff* __restrict__ bases, uint32_t n, uint32_t* __restrict__ mask) {
@@ -274,19 +286,20 @@ __global__ void msm_inf_mask_kernel(const typename C::aff* __restrict__ bases, u
     if ((threadIdx.x & 31) == 0 && i < n) mask[i >> 5] = bits;
 }
 
+
 // ---------------------------------------------------------------------------------------------------------
 // host side: workspace + staged launch
 // ---------------------------------------------------------------------------------------------------------
 struct MsmConfig {
     int c = 0;          // window bits (0 = pick from n)
-    uint32_t T = 0;     // max entries per task (0 = 4 x mean bucket load, at least 32)
+    uint32_t T = 0;     // max entries per task (0 = from the entry count: about 1024 tasks' worth of work per SM)
     uint32_t L = 16;    // buckets per reduction chunk
 };
 
 // Counters a finished MSM leaves behind (for bench.py's work model and tests)
 struct MsmStats {
     unsigned long long entries = 0;  // non-zero digits = mixed additions issued
-    uint32_t tasks = 0, cut_buckets = 0, buckets = 0;
+    uint32_t tasks = 0, cut_buckets = 0, buckets = 0, T = 0;
     int c = 0, W = 0;
 };
 
@@ -295,11 +308,15 @@ class Msm {
 public:
     typedef typename C::aff aff;
     typedef typename C::pt pt;
+    static constexpr uint32_t T_MIN = sizeof(pt) > 128 ? 16 : 32;
+    static constexpr uint32_t T_MAX = 512;
 
     Msm() {}
     ~Msm() {
         if (h_counters) cudaFreeHost(h_counters);
-        if (h_result) cudaFreeHost(h_result);
+        if (h_windows) cudaFreeHost(h_windows);
+        if (ev_acc0) cudaEventDestroy(ev_acc0);
+        if (ev_acc1) cudaEventDestroy(ev_acc1);
     }
 
     // capacity for n points
@@ -307,53 +324,47 @@ public:
         cfg = cfg_in;
         cap_n = n;
         c = cfg.c ? cfg.c : msm_pick_c(n);
+        if (c < 2) c = 2;
+        if (c > 24) c = 24;
         W = msm_num_windows(c);
         bpw = 1u << (c - 1);
         nb = uint32_t(W) * bpw;
         size_t m_max = n * size_t(W);
         if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
-        T = cfg.T;
-        if (T == 0) {
-            size_t mean = n / bpw + 1;
-            T = uint32_t(mean * 4 < 32 ? 32 : mean * 4);
-        }
         L = cfg.L;
         cpw = (bpw + L - 1) / L;
-        size_t nt_max = nb + m_max / T + 2;
-        size_t np_max = 2 * (m_max / T) + 2;
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        slots = size_t(sms) * (sizeof(pt) > 128 ? 512 : 1024);
         size_t e = m_max ? m_max : 1;
         keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_a.alloc(e * 4); vals_b.alloc(e * 4);
         start.alloc(size_t(nb) * 4); end.alloc(size_t(nb) * 4);
-        ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4);
-        task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4);
-        cut_list.alloc((m_max / T + 2) * 4);
-        t_begin.alloc(nt_max * 4); t_len.alloc(nt_max * 4); t_out.alloc(nt_max * 4);
-        tk_a.alloc(nt_max * 4); tk_b.alloc(nt_max * 4); tv_a.alloc(nt_max * 4); tv_b.alloc(nt_max * 4);
+        ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4); nblk.alloc(size_t(nb + 1) * 4);
+        task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
+        cut_list.alloc((m_max / T_MIN + 2) * 4);  // a cut bucket holds more than T >= T_MIN entries
         buckets.alloc(size_t(nb) * sizeof(pt));
-        parts.alloc(np_max * sizeof(pt));
         chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
         window_out.alloc(size_t(W) * sizeof(pt));
-        result.alloc(sizeof(pt));
         counters.alloc(64);
-        // cub temp: max over the calls we make
-        size_t t1 = 0, t2 = 0, t3 = 0;
+        size_t t1 = 0, t3 = 0;
         cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
         cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
         cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)e, 0, key_bits());
-        cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
-        cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
-        cub::DeviceRadixSort::SortPairs(nullptr, t2, tk, tv, (int)nt_max, 0, 32);
         cub::DeviceScan::ExclusiveSum(nullptr, t3, ntasks.as<uint32_t>(), task_base.as<uint32_t>(), (int)(nb + 1));
-        size_t t = t1 > t2 ? t1 : t2;
-        if (t3 > t) t = t3;
-        cub_tmp.alloc(t + 256);
+        cub_tmp.alloc((t1 > t3 ? t1 : t3) + 256);
         if (!h_counters) G16_CUDA(cudaMallocHost(&h_counters, 64));
-        if (!h_result) G16_CUDA(cudaMallocHost(&h_result, sizeof(pt)));
+        if (!h_windows) G16_CUDA(cudaMallocHost(&h_windows, 32 * sizeof(pt) * 8));
+        if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
+        if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
+        if (!ev_acc1) G16_CUDA(cudaEventCreate(&ev_acc1));
     }
 
-    size_t workspace_bytes() const {
-        return keys_a.bytes * 4 + start.bytes * 6 + t_begin.bytes * 7 + buckets.bytes + parts.bytes + chunk_out.bytes +
-               cub_tmp.bytes;
+    // duration of the last accumulate kernel (CUDA events on its own stream); valid once the stream is synchronised
+    float accumulate_ms() const {
+        float ms = 0;
+        if (!acc_timed || cudaEventElapsedTime(&ms, ev_acc0, ev_acc1) != cudaSuccess) return 0;
+        return ms;
     }
 
     // stage 1: digits (async).  scalars/bases/mask are device pointers; n <= reserved capacity.
@@ -368,17 +379,25 @@ public:
                                                                           keys_a.as<uint32_t>(), vals_a.as<uint32_t>(),
                                                                           counters.as<unsigned long long>());
             G16_CUDA(cudaGetLastError());
+            G16_LAUNCHED(1);
         }
+        acc_timed = false;
         G16_CUDA(cudaMemcpyAsync(h_counters, counters.p, 16, cudaMemcpyDeviceToHost, s));
     }
 
-    // stage 2: sort + tasks (reads the entry count -> one stream sync)
+    // stage 2: sort + task counts (reads the entry count -> one stream sync)
     void stage2() {
         cudaStream_t s = stream;
         G16_CUDA(cudaStreamSynchronize(s));
         m = (size_t)h_counters[0];
+        T = cfg.T;
+        if (T == 0) {
+            size_t t = m / slots;
+            T = uint32_t(t < T_MIN ? T_MIN : t > T_MAX ? T_MAX : t);
+        }
+        if (T < T_MIN) T = T_MIN;
         stats = MsmStats();
-        stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb;
+        stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb; stats.T = T;
         G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
         if (m == 0) return;
         cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
@@ -394,68 +413,95 @@ public:
         uint32_t* cut_count = counters.as<uint32_t>() + 4;  // byte offset 16
         msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb, T,
                                                                     ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
-                                                                    cut_list.as<uint32_t>(), cut_count);
-        tb = cub_tmp.bytes;
-        G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, ntasks.as<uint32_t>(), task_base.as<uint32_t>(),
-                                               (int)(nb + 1), s));
-        tb = cub_tmp.bytes;
-        G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, nparts.as<uint32_t>(), part_base.as<uint32_t>(),
-                                               (int)(nb + 1), s));
-        // h_counters[2] = number of tasks, [3] = number of cut buckets
-        G16_CUDA(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h_counters) + 4, task_base.as<uint32_t>() + nb, 4,
-                                 cudaMemcpyDeviceToHost, s));
-        G16_CUDA(cudaMemcpyAsync(reinterpret_cast<uint32_t*>(h_counters) + 5, cut_count, 4, cudaMemcpyDeviceToHost, s));
+                                                                    nblk.as<uint32_t>(), cut_list.as<uint32_t>(), cut_count);
+        G16_LAUNCHED(2);
+        uint32_t* src[3] = {ntasks.as<uint32_t>(), nparts.as<uint32_t>(), nblk.as<uint32_t>()};
+        uint32_t* dst[3] = {task_base.as<uint32_t>(), part_base.as<uint32_t>(), blk_base.as<uint32_t>()};
+        uint32_t* h32 = reinterpret_cast<uint32_t*>(h_counters);
+        for (int i = 0; i < 3; i++) {
+            tb = cub_tmp.bytes;
+            G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, src[i], dst[i], (int)(nb + 1), s));
+            // h32[4] = tasks, [5] = partial sums, [6] = combine blocks, [7] = cut buckets
+            G16_CUDA(cudaMemcpyAsync(h32 + 4 + i, dst[i] + nb, 4, cudaMemcpyDeviceToHost, s));
+        }
+        G16_CUDA(cudaMemcpyAsync(h32 + 7, cut_count, 4, cudaMemcpyDeviceToHost, s));
     }
 
-    // stage 3: accumulate + reductions (reads the task count -> one stream sync); result stays on the device
+    // stage 3: accumulate + reductions (reads the task count -> one stream sync); window sums go to the host
     void stage3() {
         cudaStream_t s = stream;
         if (m != 0) {
             G16_CUDA(cudaStreamSynchronize(s));
-            uint32_t nt = reinterpret_cast<uint32_t*>(h_counters)[4];
-            uint32_t ncut = reinterpret_cast<uint32_t*>(h_counters)[5];
+            const uint32_t* h32 = reinterpret_cast<const uint32_t*>(h_counters);
+            uint32_t nt = h32[4], np = h32[5], nblocks = h32[6], ncut = h32[7];
             stats.tasks = nt;
             stats.cut_buckets = ncut;
+            // the stream is idle here, so growing these is safe
+            grow(t_begin, size_t(nt) * 4); grow(t_len, size_t(nt) * 4); grow(t_out, size_t(nt) * 4);
+            grow(tk_a, size_t(nt) * 4); grow(tk_b, size_t(nt) * 4); grow(tv_a, size_t(nt) * 4); grow(tv_b, size_t(nt) * 4);
+            grow(parts, size_t(np) * sizeof(pt));
+            grow(parts2, size_t(nblocks) * sizeof(pt));
+            cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
+            cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
+            int bits = 1;
+            while ((1u << bits) <= T) bits++;
+            size_t need = 0;
+            cub::DeviceRadixSort::SortPairs(nullptr, need, tk, tv, (int)nt, 0, bits);
+            grow(task_tmp, need + 256);
             msm_make_tasks_kernel<<<(nt + 255) / 256, 256, 0, s>>>(
                 start.as<uint32_t>(), end.as<uint32_t>(), task_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, nt, T,
                 t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), tk_a.as<uint32_t>(),
                 tv_a.as<uint32_t>());
-            cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
-            cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
-            size_t tb = cub_tmp.bytes;
-            int bits = 1;
-            while ((1u << bits) <= T) bits++;
-            G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
+            size_t tb = task_tmp.bytes;
+            G16_CUDA(cub::DeviceRadixSort::SortPairs(task_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
+            G16_CUDA(cudaEventRecord(ev_acc0, s));
             msm_accumulate_kernel<C><<<(nt + 127) / 128, 128, 0, s>>>(
                 bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
                 buckets.as<pt>(), parts.as<pt>());
+            G16_CUDA(cudaEventRecord(ev_acc1, s));
+            acc_timed = true;
             G16_CUDA(cudaGetLastError());
+            G16_LAUNCHED(2);
             if (ncut) {
-                msm_combine_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
-                    cut_list.as<uint32_t>(), part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
+                msm_combine1_kernel<C, RED_THREADS><<<nblocks, RED_THREADS, 0, s>>>(
+                    blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, parts.as<pt>(), parts2.as<pt>());
+                msm_combine2_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
+                    cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), parts2.as<pt>(), buckets.as<pt>());
                 G16_CUDA(cudaGetLastError());
+                G16_LAUNCHED(2);
             }
         }
         uint32_t nchunks = uint32_t(W) * cpw;
         msm_chunk_reduce_kernel<C><<<(nchunks + 63) / 64, 64, 0, s>>>(buckets.as<pt>(), bpw, L, cpw, nchunks,
                                                                       chunk_out.as<pt>());
-        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(chunk_out.as<pt>(), cpw,
-                                                                                              window_out.as<pt>());
-        msm_horner_kernel<C><<<1, 32, 0, s>>>(window_out.as<pt>(), W, c, result.as<pt>());
+        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(chunk_out.as<pt>(), cpw, window_out.as<pt>());
         G16_CUDA(cudaGetLastError());
-        G16_CUDA(cudaMemcpyAsync(h_result, result.p, sizeof(pt), cudaMemcpyDeviceToHost, s));
+        G16_LAUNCHED(2);
+        G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));
     }
 
-    // whole MSM on one stream; returns after the result is in host memory
-    const pt* run(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
+    // whole MSM on one stream; returns after the window sums are in host memory
+    void run(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
         stage1(bases_, scalars, inf_mask, n_, s);
         stage2();
         stage3();
         G16_CUDA(cudaStreamSynchronize(s));
-        return h_result;
     }
-    const pt* host_result() const { return h_result; }  // valid after the stream is synchronised
-    const pt* device_result() const { return result.as<pt>(); }
+
+    // sum_w 2^(c w) S_w on the host (255 dependent doublings: a latency chain, an order of magnitude quicker on a
+    // CPU core than on one GPU thread).  HC = g16h::HG1 / HG2, whose XYZZ layout equals the device one.
+    // Valid after the stream is synchronised.
+    template <class HC>
+    typename HC::pt finish() const {
+        static_assert(sizeof(typename HC::pt) == sizeof(pt), "host/device point layouts differ");
+        typename HC::pt acc = HC::identity(), sw;
+        for (int w = W - 1; w >= 0; w--) {
+            for (int i = 0; i < c; i++) acc = HC::dbl(acc);
+            std::memcpy(&sw, h_windows + w, sizeof(pt));
+            acc = HC::add(acc, sw);
+        }
+        return acc;
+    }
     static void prepare() {}
 
     MsmStats stats;
@@ -464,21 +510,27 @@ public:
 
 private:
     static constexpr int RED_THREADS = 128;
+    static void grow(DevBuf& b, size_t bytes) {
+        if (bytes > b.bytes) b.alloc(bytes + bytes / 4 + 4096);
+    }
     int key_bits() const {
         int b = 1;
         while ((size_t(1) << b) < nb) b++;
         return b;
     }
     MsmConfig cfg;
-    size_t cap_n = 0, n = 0, m = 0;
+    size_t cap_n = 0, n = 0, m = 0, slots = 148 * 1024;
     uint32_t bpw = 0, nb = 0, cpw = 0;
     const aff* bases = nullptr;
     cudaStream_t stream = 0;
     uint32_t *sorted_keys = nullptr, *sorted_vals = nullptr;
-    DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, task_base, part_base, cut_list, t_begin, t_len,
-        t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, chunk_out, window_out, result, counters, cub_tmp;
+    DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
+        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, chunk_out, window_out, counters, cub_tmp,
+        task_tmp;
     unsigned long long* h_counters = nullptr;
-    pt* h_result = nullptr;
+    pt* h_windows = nullptr;
+    cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr;
+    bool acc_timed = false;
 };
 
 #ifndef G16_MSM_INSTANTIATE

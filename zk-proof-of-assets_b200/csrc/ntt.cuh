@@ -196,6 +196,7 @@ struct NttDomain {
             sl += ks[i];
         }
         G16_CUDA(cudaGetLastError());
+        G16_LAUNCHED(2 * ks.size());
     }
 
     // plain transforms (test hooks / standalone operator): natural order in and out is NOT provided by a single call;

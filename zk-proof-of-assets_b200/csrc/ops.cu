@@ -44,9 +44,7 @@ void use_device(const g16_opts* o) {
     if (o && o->device >= 0) G16_CUDA(cudaSetDevice(o->device));
 }
 
-void g1_out(const g1_pt* r, uint8_t* out) {
-    HPoint<HFq> p{u256_from_bytes((const uint8_t*)&r->x), u256_from_bytes((const uint8_t*)&r->y),
-                  u256_from_bytes((const uint8_t*)&r->zz), u256_from_bytes((const uint8_t*)&r->zzz)};
+void g1_out(const HPoint<HFq>& p, uint8_t* out) {
     HAffine<HFq> a = HG1::to_affine(p);
     std::memset(out, 0, 64);
     if (!a.inf) {
@@ -54,13 +52,7 @@ void g1_out(const g1_pt* r, uint8_t* out) {
         u256_to_bytes(a.y, out + 32);
     }
 }
-void g2_out(const g2_pt* r, uint8_t* out) {
-    const uint8_t* b = (const uint8_t*)r;
-    HPoint<HFq2> p;
-    p.x = HFq2El{u256_from_bytes(b), u256_from_bytes(b + 32)};
-    p.y = HFq2El{u256_from_bytes(b + 64), u256_from_bytes(b + 96)};
-    p.zz = HFq2El{u256_from_bytes(b + 128), u256_from_bytes(b + 160)};
-    p.zzz = HFq2El{u256_from_bytes(b + 192), u256_from_bytes(b + 224)};
+void g2_out(const HPoint<HFq2>& p, uint8_t* out) {
     HAffine<HFq2> a = HG2::to_affine(p);
     std::memset(out, 0, 128);
     if (!a.inf) {
@@ -69,6 +61,16 @@ void g2_out(const g2_pt* r, uint8_t* out) {
         u256_to_bytes(a.y.c0, out + 64);
         u256_to_bytes(a.y.c1, out + 96);
     }
+}
+void g1_out(const g1_pt* r, uint8_t* out) {
+    HPoint<HFq> p;
+    std::memcpy(&p, r, sizeof(p));
+    g1_out(p, out);
+}
+void g2_out(const g2_pt* r, uint8_t* out) {
+    HPoint<HFq2> p;
+    std::memcpy(&p, r, sizeof(p));
+    g2_out(p, out);
 }
 
 // ---- micro-operator kernels ---------------------------------------------------------------------------------
@@ -240,10 +242,12 @@ int g16_msm_run_dev(g16_msm* m, const void* d_bases, const void* d_scalars, size
         unsigned grid = (unsigned)((n + 255) / 256);
         if (m->is_g2) {
             if (fresh && n) msm_inf_mask_kernel<G2><<<grid, 256, 0, m->s>>>((const g2_aff*)d_bases, (uint32_t)n, m->mask.as<uint32_t>());
-            g2_out(m->m2.run((const g2_aff*)d_bases, (const uint32_t*)d_scalars, m->mask.as<uint32_t>(), n, m->s), out_affine);
+            m->m2.run((const g2_aff*)d_bases, (const uint32_t*)d_scalars, m->mask.as<uint32_t>(), n, m->s);
+            g2_out(m->m2.finish<HG2>(), out_affine);
         } else {
             if (fresh && n) msm_inf_mask_kernel<G1><<<grid, 256, 0, m->s>>>((const g1_aff*)d_bases, (uint32_t)n, m->mask.as<uint32_t>());
-            g1_out(m->m1.run((const g1_aff*)d_bases, (const uint32_t*)d_scalars, m->mask.as<uint32_t>(), n, m->s), out_affine);
+            m->m1.run((const g1_aff*)d_bases, (const uint32_t*)d_scalars, m->mask.as<uint32_t>(), n, m->s);
+            g1_out(m->m1.finish<HG1>(), out_affine);
         }
         return (int)G16_OK;
     });
@@ -281,13 +285,15 @@ static int msm_host(int is_g2, const uint8_t* bases, const uint8_t* scalars, siz
                 Msm<G2> m;
                 m.reserve(n ? n : 1, cfg);
                 if (n) msm_inf_mask_kernel<G2><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(db.as<g2_aff>(), (uint32_t)n, mask.as<uint32_t>());
-                g2_out(m.run(db.as<g2_aff>(), ds.as<uint32_t>(), mask.as<uint32_t>(), n, s), out);
+                m.run(db.as<g2_aff>(), ds.as<uint32_t>(), mask.as<uint32_t>(), n, s);
+                g2_out(m.finish<HG2>(), out);
             } else {
                 Msm<G1>::prepare();
                 Msm<G1> m;
                 m.reserve(n ? n : 1, cfg);
                 if (n) msm_inf_mask_kernel<G1><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(db.as<g1_aff>(), (uint32_t)n, mask.as<uint32_t>());
-                g1_out(m.run(db.as<g1_aff>(), ds.as<uint32_t>(), mask.as<uint32_t>(), n, s), out);
+                m.run(db.as<g1_aff>(), ds.as<uint32_t>(), mask.as<uint32_t>(), n, s);
+                g1_out(m.finish<HG1>(), out);
             }
         } catch (...) {
             cudaStreamDestroy(s);
