@@ -13,7 +13,7 @@ $(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 
 $(PKG)/libg16b200.so: $(OBJS)
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -lcudart -lpthread
 
 $(PKG)/libg16synth.so: $(CSRC)/synth.o
 	$(NVCC) $(ARCH) -shared -o $@ $< -lcudart

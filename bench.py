@@ -274,6 +274,7 @@ def run_b200(args):
             "msm_mpts_per_s": msm_points / (msm_ms * 1e-3) / 1e6 if msm_ms else None,
             "phases_ms": {k: v / steps for k, v in phase.items()},
             "msm": {k: dict(v, accumulate_ms=acc_ms[k] / steps) for k, v in stats.items()},
+            "trace_last_step_ms": zk.trace(),
             "zkey_open_s": t_open,
             "clocks": clk,
             "e2e": {"value": ncons * steps * world / e2e_s, "unit": "constraints/s", "ms_per_step": e2e_s / steps * 1e3,

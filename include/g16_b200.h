@@ -123,6 +123,9 @@ int g16_last_msm_stats(const g16_zkey* zk, uint64_t out[25]);
 /* duration of the bucket-accumulation kernel (the dominant kernel) of each MSM of the last prove, milliseconds,
  * CUDA events on the stream the kernel ran on: A, B1, B2, C, H */
 int g16_last_accumulate_ms(const g16_zkey* zk, double out[5]);
+/* device timeline of the last prove, milliseconds after its start, per MSM (A, B1, B2, C, H) x { MSM starts, digits
+ * done, sort + task counts done, accumulate starts, accumulate done, window sums on the host }; -1 = not reached */
+int g16_last_trace(const g16_zkey* zk, double out[30]);
 /* cumulative number of this library's own kernel launches in this process (library kernels such as cub's are
  * not counted) */
 unsigned long long g16_launch_count(void);

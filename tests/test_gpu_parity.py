@@ -352,3 +352,45 @@ def test_prove_closed_form_at_scale(pkg, n_vars, n_public, n_cons):
         assert V.verify(sy.vkey(), json.loads(u2), json.loads(p2))
         st = zk.msm_stats()
         assert st["H"]["additions"] > 0 and st["B2"]["additions"] > 0
+
+
+SHARD_WORKER = r'''
+import os, sys, json
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+import torch.distributed as dist
+from conftest import load_pkg
+pkg = load_pkg()
+dist.init_process_group("gloo")          # two ranks share cuda:0 in the test, so the gather runs over gloo
+rank, world = dist.get_rank(), dist.get_world_size()
+zkey = open(sys.argv[2], "rb").read(); wtns = open(sys.argv[3], "rb").read()
+zk = pkg.ZKey(zkey, device=0, shard_rank=rank, shard_count=world)
+proof, public = pkg.prove_sharded(zk, wtns, r=424242, s=171717)
+open(sys.argv[4] + ".%d" % rank, "w").write(proof + "\n" + public)
+zk.close()
+dist.barrier(); dist.destroy_process_group()
+'''
+
+
+def test_prove_sharded_two_ranks(pkg, small_fixture, tmp_path):
+    """One proof over two ranks (base-range shards, 768-byte partial gather) == the whole-key proof, on every rank."""
+    import socket
+    import sys
+    f = small_fixture
+    (tmp_path / "k.zkey").write_bytes(bytes(f["zkey_bytes"]))
+    (tmp_path / "w.wtns").write_bytes(bytes(f["wtns_bytes"]))
+    (tmp_path / "worker.py").write_text(SHARD_WORKER)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(tmp_path / "worker.py"), ROOT, str(tmp_path / "k.zkey"),
+                                       str(tmp_path / "w.wtns"), str(tmp_path / "out")], env=env,
+                                      stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    for p in procs:
+        out = p.communicate(timeout=300)[0]
+        assert p.returncode == 0, out
+    want = "\n".join(g16.prove(f["zk"], f["w"], 424242, 171717))
+    for rank in range(2):
+        assert (tmp_path / ("out.%d" % rank)).read_text() == want

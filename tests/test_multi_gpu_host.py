@@ -1,0 +1,65 @@
+"""Host-side logic of the multi-GPU path on CPU: shard ranges and the partial gather over a world_size-2 gloo group."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+from conftest import ROOT, load_pkg
+
+
+def test_shard_ranges_partition_every_section():
+    pkg = load_pkg()
+    for n in (0, 1, 7, 2083343, 2097152):
+        for count in (1, 2, 3, 4, 8):
+            r = [pkg.shard_range(n, k, count) for k in range(count)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(r[i][1] == r[i + 1][0] for i in range(count - 1))
+            sizes = [hi - lo for lo, hi in r]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        pkg.shard_range(10, 2, 2)
+
+
+WORKER = r'''
+import os, sys
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+import torch.distributed as dist
+from conftest import load_pkg
+pkg = load_pkg()
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+mine = bytes([(rank * 37 + i) % 251 for i in range(pkg.PARTIAL_BYTES)])
+allp = pkg.all_gather_partials(mine)
+assert len(allp) == world * pkg.PARTIAL_BYTES
+for k in range(world):
+    want = bytes([(k * 37 + i) % 251 for i in range(pkg.PARTIAL_BYTES)])
+    assert allp[k * pkg.PARTIAL_BYTES:(k + 1) * pkg.PARTIAL_BYTES] == want, k
+try:
+    pkg.all_gather_partials(b"short")
+    raise SystemExit("expected ValueError")
+except ValueError:
+    pass
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
+def test_partial_gather_gloo_world2(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port))
+        procs.append(subprocess.Popen([sys.executable, str(script), ROOT], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=180)[0] for p in procs]
+    for rank, (p, o) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, o
+        assert "rank %d ok" % rank in o

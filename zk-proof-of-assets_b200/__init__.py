@@ -36,7 +36,7 @@ ABI_SYMBOLS = [
     "g16_prove_combine", "g16_msm_g1_host", "g16_msm_g2_host", "g16_msm_create", "g16_msm_destroy", "g16_msm_run_dev",
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
-    "g16_last_accumulate_ms", "g16_launch_count",
+    "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -103,6 +103,7 @@ def lib():
         L.g16_bench_int_pipe.argtypes = [ctypes.c_int, ctypes.c_void_p]
         L.g16_last_accumulate_ms.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.g16_launch_count.restype = ctypes.c_ulonglong
+        L.g16_last_trace.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -247,6 +248,13 @@ class ZKey:
         t = (ctypes.c_double * 5)()
         _check(lib().g16_last_accumulate_ms(self._h, t))
         return dict(zip(["A", "B1", "B2", "C", "H"], list(t)))
+
+    def trace(self):
+        """device timeline of the last prove: per MSM, ms after the prove started"""
+        t = (ctypes.c_double * 30)()
+        _check(lib().g16_last_trace(self._h, t))
+        keys = ["start", "digits_done", "sorted", "acc_start", "acc_done", "done"]
+        return {n: dict(zip(keys, [round(x, 3) for x in t[6 * i:6 * i + 6]])) for i, n in enumerate(["A", "B1", "B2", "C", "H"])}
 
     def msm_stats(self):
         t = (ctypes.c_uint64 * 25)()
@@ -414,3 +422,37 @@ def fixed_base(is_g2, scalars, n):
     if synth_lib().g16_synth_fixed_base(int(is_g2), bytes(scalars), n, out):
         raise RuntimeError(synth_lib().g16_synth_last_error().decode())
     return out.raw
+
+
+# ---- multi-GPU host logic (SURVEY.md section 8(e)) ----------------------------------------------------------
+def shard_range(n, rank, count):
+    """[lo, hi) of a section of n points held by shard `rank` of `count` -- the rule libg16b200 applies at
+    g16_zkey_open (contiguous base ranges, sizes differing by at most one)."""
+    if not 0 <= rank < count:
+        raise ValueError("bad shard rank")
+    return n * rank // count, n * (rank + 1) // count
+
+
+def all_gather_partials(partial, group=None):
+    """The one exchange step of a sharded proof: every rank contributes its 768-byte partial (five XYZZ partial
+    sums), every rank receives all of them in rank order.  torch.distributed is plumbing here: NCCL on GPUs
+    (768 B per rank over NVLink), gloo in the CPU tests."""
+    import torch
+    import torch.distributed as dist
+    if len(partial) != PARTIAL_BYTES:
+        raise ValueError("a partial is %d bytes" % PARTIAL_BYTES)
+    world = dist.get_world_size(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    mine = torch.frombuffer(bytearray(partial), dtype=torch.uint8).to(dev)
+    out = torch.empty(world * PARTIAL_BYTES, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(out, mine, group=group)
+    return out.cpu().numpy().tobytes()
+
+
+def prove_sharded(zk, wtns, r=None, s=None, style=STYLE_RAPIDSNARK, group=None):
+    """One proof over all ranks of `group`: zk was opened with shard_rank = rank, shard_count = world size.
+    Every rank returns the same (proof.json, public.json); r, s must be equal on all ranks (pinned, or drawn by
+    rank 0 and broadcast by the caller)."""
+    zk.load_witness(wtns)
+    partials = all_gather_partials(zk.prove_partial(), group)
+    return zk.combine(partials, r=r, s=s, style=style)

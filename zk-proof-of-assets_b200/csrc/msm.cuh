@@ -114,6 +114,7 @@ static __global__ void msm_bounds_kernel(const uint32_t* __restrict__ keys, uint
 // per bucket: number of tasks, number of partial-sum slots (0 unless the bucket is cut), number of first-level
 // combine blocks (COMBINE_GROUP partial sums each), list of cut buckets
 constexpr uint32_t COMBINE_GROUP = 1024;
+constexpr uint32_t COMBINE_SMALL = 16;  // cut buckets with at most this many partial sums are summed by one thread
 static __global__ void msm_count_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end, uint32_t nb,
                                        uint32_t T, uint32_t* __restrict__ ntasks, uint32_t* __restrict__ nparts,
                                        uint32_t* __restrict__ nblk, uint32_t* __restrict__ cut_list,
@@ -124,7 +125,7 @@ static __global__ void msm_count_tasks_kernel(const uint32_t* __restrict__ start
     if (k < nb) t = (end[k] - start[k] + T - 1) / T;
     ntasks[k] = t;
     nparts[k] = t > 1 ? t : 0;
-    nblk[k] = t > 1 ? (t + COMBINE_GROUP - 1) / COMBINE_GROUP : 0;
+    nblk[k] = t > COMBINE_SMALL ? (t + COMBINE_GROUP - 1) / COMBINE_GROUP : 0;
     if (t > 1) cut_list[atomicAdd(cut_count, 1u)] = k;
 }
 
@@ -212,7 +213,22 @@ __device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
     acc = sh[0];
 }
 
-// Cut buckets are summed in two levels so that a bucket holding a quarter of all points (the digit-1 bucket of a
+// Most cut buckets hold a handful of partial sums (a bucket a few times over the task size): one thread each.
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_combine_small_kernel(const uint32_t* __restrict__ cut_list, uint32_t ncut, const uint32_t* __restrict__ part_base,
+                         const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ buckets) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= ncut) return;
+    uint32_t k = cut_list[i];
+    uint32_t b = part_base[k], e = part_base[k + 1];
+    if (e - b > COMBINE_SMALL) return;
+    typename C::pt acc = parts[b];
+    for (uint32_t j = b + 1; j < e; j++) C::add(acc, parts[j]);
+    buckets[k] = acc;
+}
+
+// The heavy cut buckets are summed in two levels so that a bucket holding a quarter of all points (the digit-1 bucket of a
 // circom witness) is still a short dependency chain: level 1 = one CTA per COMBINE_GROUP partial sums,
 // level 2 = one CTA per cut bucket over its level-1 results.
 template <class C, int THREADS>
@@ -236,6 +252,7 @@ msm_combine2_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __res
     uint32_t k = cut_list[blockIdx.x];
     uint32_t b = blk_base[k], e = blk_base[k + 1];
     typename C::pt acc = C::identity();
+    if (e == b) return;  // a small cut bucket: msm_combine_small_kernel wrote it
     for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts2[i]);
     block_sum_points<C, THREADS>(acc);
     if (threadIdx.x == 0) buckets[k] = acc;
@@ -290,7 +307,16 @@ __global__ void msm_inf_mask_kernel(const typename C::aff* __restrict__ bases, u
 // ---------------------------------------------------------------------------------------------------------
 // host side: workspace + staged launch
 // ---------------------------------------------------------------------------------------------------------
+// Witness-scalar MSMs (A, B1, B2, C): most scalars are 0/1 or below 2^64, so there is about one non-zero digit per
+// point instead of W; narrower windows keep the bucket reduction (2 full additions per bucket per window) in
+// proportion.  Measured on c2-layer-one: c = 15 -> 12 shrinks 278 K buckets to 45 K for 25 % more additions.
+static inline int msm_pick_c_sparse(size_t n) {
+    int c = msm_pick_c(n) - 3;
+    return c < 6 ? 6 : c;
+}
+
 struct MsmConfig {
+    bool sparse = false;  // scalars are witness-like (see msm_pick_c_sparse)
     int c = 0;          // window bits (0 = pick from n)
     uint32_t T = 0;     // max entries per task (0 = from the entry count: about 1024 tasks' worth of work per SM)
     uint32_t L = 16;    // buckets per reduction chunk
@@ -317,13 +343,15 @@ public:
         if (h_windows) cudaFreeHost(h_windows);
         if (ev_acc0) cudaEventDestroy(ev_acc0);
         if (ev_acc1) cudaEventDestroy(ev_acc1);
+        for (auto& e : ev_t)
+            if (e) cudaEventDestroy(e);
     }
 
     // capacity for n points
     void reserve(size_t n, const MsmConfig& cfg_in = MsmConfig()) {
         cfg = cfg_in;
         cap_n = n;
-        c = cfg.c ? cfg.c : msm_pick_c(n);
+        c = cfg.c ? cfg.c : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
         if (c < 2) c = 2;
         if (c > 24) c = 24;
         W = msm_num_windows(c);
@@ -358,6 +386,20 @@ public:
         if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
         if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
         if (!ev_acc1) G16_CUDA(cudaEventCreate(&ev_acc1));
+        for (auto& e : ev_t)
+            if (!e) G16_CUDA(cudaEventCreate(&e));
+    }
+
+    // timeline of the last run relative to `base` (an event recorded earlier), milliseconds:
+    // [0] start, [1] digits done, [2] sort + task counts done, [3] accumulate starts, [4] accumulate done, [5] window sums on the host
+    void trace(cudaEvent_t base, float out[6]) const {
+        cudaEvent_t e[6] = {ev_t[0], ev_t[1], ev_t[2], ev_acc0, ev_acc1, ev_t[3]};
+        for (int i = 0; i < 6; i++) {
+            out[i] = -1;
+            if ((i == 3 || i == 4) && !acc_timed) continue;
+            float ms = 0;
+            if (cudaEventElapsedTime(&ms, base, e[i]) == cudaSuccess) out[i] = ms;
+        }
     }
 
     // duration of the last accumulate kernel (CUDA events on its own stream); valid once the stream is synchronised
@@ -373,6 +415,7 @@ public:
         bases = bases_;
         n = n_;
         stream = s;
+        G16_CUDA(cudaEventRecord(ev_t[0], s));
         G16_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
         if (n) {
             msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, W,
@@ -382,6 +425,7 @@ public:
             G16_LAUNCHED(1);
         }
         acc_timed = false;
+        G16_CUDA(cudaEventRecord(ev_t[1], s));
         G16_CUDA(cudaMemcpyAsync(h_counters, counters.p, 16, cudaMemcpyDeviceToHost, s));
     }
 
@@ -392,6 +436,8 @@ public:
         m = (size_t)h_counters[0];
         T = cfg.T;
         if (T == 0) {
+            // enough tasks to fill the machine several times over: a task is one thread's dependency chain, so its
+            // length bounds the kernel's tail; a cut bucket costs one extra full addition per task
             size_t t = m / slots;
             T = uint32_t(t < T_MIN ? T_MIN : t > T_MAX ? T_MAX : t);
         }
@@ -399,7 +445,10 @@ public:
         stats = MsmStats();
         stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb; stats.T = T;
         G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
-        if (m == 0) return;
+        if (m == 0) {
+            G16_CUDA(cudaEventRecord(ev_t[2], s));
+            return;
+        }
         cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
         cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
         size_t tb = cub_tmp.bytes;
@@ -425,6 +474,7 @@ public:
             G16_CUDA(cudaMemcpyAsync(h32 + 4 + i, dst[i] + nb, 4, cudaMemcpyDeviceToHost, s));
         }
         G16_CUDA(cudaMemcpyAsync(h32 + 7, cut_count, 4, cudaMemcpyDeviceToHost, s));
+        G16_CUDA(cudaEventRecord(ev_t[2], s));
     }
 
     // stage 3: accumulate + reductions (reads the task count -> one stream sync); window sums go to the host
@@ -463,12 +513,17 @@ public:
             G16_CUDA(cudaGetLastError());
             G16_LAUNCHED(2);
             if (ncut) {
-                msm_combine1_kernel<C, RED_THREADS><<<nblocks, RED_THREADS, 0, s>>>(
-                    blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, parts.as<pt>(), parts2.as<pt>());
-                msm_combine2_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
-                    cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), parts2.as<pt>(), buckets.as<pt>());
+                msm_combine_small_kernel<C><<<(ncut + 127) / 128, 128, 0, s>>>(
+                    cut_list.as<uint32_t>(), ncut, part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
+                G16_LAUNCHED(1);
+                if (nblocks) {
+                    msm_combine1_kernel<C, RED_THREADS><<<nblocks, RED_THREADS, 0, s>>>(
+                        blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, parts.as<pt>(), parts2.as<pt>());
+                    msm_combine2_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
+                        cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), parts2.as<pt>(), buckets.as<pt>());
+                    G16_LAUNCHED(2);
+                }
                 G16_CUDA(cudaGetLastError());
-                G16_LAUNCHED(2);
             }
         }
         uint32_t nchunks = uint32_t(W) * cpw;
@@ -478,6 +533,7 @@ public:
         G16_CUDA(cudaGetLastError());
         G16_LAUNCHED(2);
         G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));
+        G16_CUDA(cudaEventRecord(ev_t[3], s));
     }
 
     // whole MSM on one stream; returns after the window sums are in host memory
@@ -529,7 +585,7 @@ private:
         task_tmp;
     unsigned long long* h_counters = nullptr;
     pt* h_windows = nullptr;
-    cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr;
+    cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr, ev_t[4] = {nullptr, nullptr, nullptr, nullptr};
     bool acc_timed = false;
 };
 

@@ -9,6 +9,7 @@
 #include <unistd.h>
 
 #include <chrono>
+#include <future>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -219,7 +220,7 @@ static void set_device(int device) {
 
 template <class C>
 static void load_section(BaseSection<C>& sec, const Section& s, size_t rec, size_t expect, int rank, int count,
-                         int msm_c, cudaStream_t st, const char* name) {
+                         int msm_c, bool sparse, cudaStream_t st, const char* name) {
     if (s.size != expect * rec) throw FormatError(std::string("zkey: section ") + name + " has the wrong size");
     sec.lo = expect * size_t(rank) / size_t(count);
     size_t hi = expect * size_t(rank + 1) / size_t(count);
@@ -234,6 +235,7 @@ static void load_section(BaseSection<C>& sec, const Section& s, size_t rec, size
     }
     MsmConfig cfg;
     cfg.c = msm_c;
+    cfg.sparse = sparse;
     sec.msm.reserve(sec.n ? sec.n : 1, cfg);
 }
 
@@ -276,8 +278,15 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     zk->delta1 = dec_g1(p + 128 + 128 + 128);
     zk->delta2 = dec_g2(p + 128 + 128 + 128 + 64);
 
-    G16_CUDA(cudaStreamCreateWithFlags(&zk->s_main, cudaStreamNonBlocking));
-    for (auto& s : zk->s_msm) G16_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    // Priorities order the throughput-bound work so that the latency-bound tails overlap it: transforms first (they
+    // gate the H MSM), then the witness-scalar MSMs, whose bucket reductions (short dependency chains on few
+    // threads) then run while the H accumulation, lowest, fills the machine.
+    int prio_lo = 0, prio_hi = 0;
+    G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    int prio_mid = prio_hi < prio_lo - 1 ? prio_hi + 1 : prio_hi;
+    G16_CUDA(cudaStreamCreateWithPriority(&zk->s_main, cudaStreamNonBlocking, prio_hi));
+    for (int i = 0; i < 5; i++)
+        G16_CUDA(cudaStreamCreateWithPriority(&zk->s_msm[i], cudaStreamNonBlocking, i == 4 ? prio_lo : prio_mid));
     for (auto& e : zk->ev) G16_CUDA(cudaEventCreate(&e));
     zk->ev_ok = true;
     Msm<G1>::prepare();
@@ -286,12 +295,12 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
 
     // sections 5-9: base points (this shard's slice)
     size_t nv = zk->n_vars;
-    load_section<G1>(zk->A, need(secs, 5, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, st, "5 (A)");
-    load_section<G1>(zk->B1, need(secs, 6, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, st, "6 (B1)");
-    load_section<G2>(zk->B2, need(secs, 7, "zkey"), 128, nv, zk->shard_rank, zk->shard_count, o.msm_c, st, "7 (B2)");
+    load_section<G1>(zk->A, need(secs, 5, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "5 (A)");
+    load_section<G1>(zk->B1, need(secs, 6, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "6 (B1)");
+    load_section<G2>(zk->B2, need(secs, 7, "zkey"), 128, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "7 (B2)");
     load_section<G1>(zk->C, need(secs, 8, "zkey"), 64, nv - zk->n_public - 1, zk->shard_rank, zk->shard_count, o.msm_c,
-                     st, "8 (C)");
-    load_section<G1>(zk->H, need(secs, 9, "zkey"), 64, n, zk->shard_rank, zk->shard_count, o.msm_c, st, "9 (H)");
+                     true, st, "8 (C)");
+    load_section<G1>(zk->H, need(secs, 9, "zkey"), 64, n, zk->shard_rank, zk->shard_count, o.msm_c, false, st, "9 (H)");
 
     // section 4: coefficients -> CSR by (matrix, constraint)
     const Section& s4 = need(secs, 4, "zkey");
@@ -504,13 +513,35 @@ static void prove_device(g16_zkey* zk) {
     G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_msm[4]));
     zk->H.msm.stage1(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
                      zk->s_msm[4]);
-    // the witness-scalar MSMs are fully enqueued before the host first waits on the H stream (NTT pipeline + digits),
-    // so their accumulation overlaps the transforms; B2 (G2, the longest of the four) goes first
-    zk->B2.msm.stage2(); zk->A.msm.stage2(); zk->B1.msm.stage2(); zk->C.msm.stage2();
-    zk->B2.msm.stage3(); zk->A.msm.stage3(); zk->B1.msm.stage3(); zk->C.msm.stage3();
-    zk->H.msm.stage2();
-    zk->H.msm.stage3();
-    for (int i = 0; i < 5; i++) G16_CUDA(cudaEventRecord(zk->ev[4 + 2 * i], zk->s_msm[i]));
+    // Each MSM has two points where the host must read a counter back (entry count, task count).  One host thread
+    // per MSM drives those, so a wait on one stream never delays the launches of another (the H chain in particular
+    // must be enqueued the moment the transforms finish).
+    int dev = zk->device;
+    auto drive = [dev](auto* msm, cudaStream_t st, cudaEvent_t done) {
+        G16_CUDA(cudaSetDevice(dev));
+        msm->stage2();
+        msm->stage3();
+        G16_CUDA(cudaEventRecord(done, st));
+        G16_CUDA(cudaStreamSynchronize(st));
+    };
+    auto f0 = std::async(std::launch::async, [&] { drive(&zk->A.msm, zk->s_msm[0], zk->ev[4]); });
+    auto f1 = std::async(std::launch::async, [&] { drive(&zk->B1.msm, zk->s_msm[1], zk->ev[6]); });
+    auto f2 = std::async(std::launch::async, [&] { drive(&zk->B2.msm, zk->s_msm[2], zk->ev[8]); });
+    auto f3 = std::async(std::launch::async, [&] { drive(&zk->C.msm, zk->s_msm[3], zk->ev[10]); });
+    std::exception_ptr err;
+    try {
+        drive(&zk->H.msm, zk->s_msm[4], zk->ev[12]);
+    } catch (...) {
+        err = std::current_exception();
+    }
+    for (auto* f : {&f0, &f1, &f2, &f3}) {
+        try {
+            f->get();
+        } catch (...) {
+            if (!err) err = std::current_exception();
+        }
+    }
+    if (err) std::rethrow_exception(err);
     for (int i = 0; i < 5; i++) G16_CUDA(cudaStreamSynchronize(zk->s_msm[i]));
     G16_CUDA(cudaStreamSynchronize(zk->s_main));
     float ms = 0;
@@ -526,9 +557,13 @@ static void prove_device(g16_zkey* zk) {
 
 static void export_partial(g16_zkey* zk, uint8_t* out) {
     auto t0 = std::chrono::steady_clock::now();
-    HPoint<HFq> a = zk->A.msm.finish<HG1>(), b1 = zk->B1.msm.finish<HG1>(), c = zk->C.msm.finish<HG1>(),
-                h = zk->H.msm.finish<HG1>();
+    // five independent Horner chains (255 doublings each); the G2 one is the longest, so it gets this thread
+    auto fa = std::async(std::launch::async, [zk] { return zk->A.msm.finish<HG1>(); });
+    auto fb = std::async(std::launch::async, [zk] { return zk->B1.msm.finish<HG1>(); });
+    auto fc = std::async(std::launch::async, [zk] { return zk->C.msm.finish<HG1>(); });
+    auto fh = std::async(std::launch::async, [zk] { return zk->H.msm.finish<HG1>(); });
     HPoint<HFq2> b2 = zk->B2.msm.finish<HG2>();
+    HPoint<HFq> a = fa.get(), b1 = fb.get(), c = fc.get(), h = fh.get();
     std::memcpy(out, &a, 128);
     std::memcpy(out + 128, &b1, 128);
     std::memcpy(out + 256, &c, 128);
@@ -563,9 +598,38 @@ static U256 random_scalar() {  // row a14: uniform in Fr by rejection
     }
 }
 
-// row a15 + a16
-static void combine(g16_zkey* zk, const uint8_t* partials, int count, const g16_opts& o, std::string& proof,
-                    std::string& pub) {
+// row a14 + the part of row a15 that does not depend on the MSM results: r, s and the multiples of delta.
+// Computed on host threads while the GPU works.
+struct Blind {
+    U256 r, s;
+    HPoint<HFq> rd1, sd1, rsd1;
+    HPoint<HFq2> sd2;
+};
+static Blind make_blind(const g16_zkey* zk, const g16_opts& o) {
+    Blind b;
+    if (o.has_rs) {
+        b.r = reduce_scalar(u256_from_bytes(o.r));
+        b.s = reduce_scalar(u256_from_bytes(o.s));
+    } else {
+        b.r = random_scalar();
+        b.s = random_scalar();
+    }
+    U256 rs = HFr::from_mont(HFr::mul(HFr::to_mont(b.r), HFr::to_mont(b.s)));
+    HPoint<HFq> d1 = HG1::from_affine(zk->delta1);
+    HPoint<HFq2> d2 = HG2::from_affine(zk->delta2);
+    auto f1 = std::async(std::launch::async, [&] { return HG1::mul(d1, b.r); });
+    auto f2 = std::async(std::launch::async, [&] { return HG1::mul(d1, b.s); });
+    auto f3 = std::async(std::launch::async, [&] { return HG1::mul(d1, rs); });
+    b.sd2 = HG2::mul(d2, b.s);
+    b.rd1 = f1.get();
+    b.sd1 = f2.get();
+    b.rsd1 = f3.get();
+    return b;
+}
+
+// rest of row a15 + row a16
+static void combine(g16_zkey* zk, const uint8_t* partials, int count, const g16_opts& o, const Blind& bl,
+                    std::string& proof, std::string& pub) {
     auto t0 = std::chrono::steady_clock::now();
     HPoint<HFq> a = HG1::identity(), b1 = a, c = a, h = a;
     HPoint<HFq2> b2 = HG2::identity();
@@ -577,24 +641,19 @@ static void combine(g16_zkey* zk, const uint8_t* partials, int count, const g16_
         h = HG1::add(h, g1_from_xyzz(p + 384));
         b2 = HG2::add(b2, g2_from_xyzz(p + 512));
     }
-    U256 r, s;
-    if (o.has_rs) {
-        r = reduce_scalar(u256_from_bytes(o.r));
-        s = reduce_scalar(u256_from_bytes(o.s));
-    } else {
-        r = random_scalar();
-        s = random_scalar();
-    }
-    U256 rs = HFr::from_mont(HFr::mul(HFr::to_mont(r), HFr::to_mont(s)));
-    HPoint<HFq> d1 = HG1::from_affine(zk->delta1);
-    HPoint<HFq> pi_a = HG1::add(HG1::add(a, HG1::from_affine(zk->alpha1)), HG1::mul(d1, r));
-    HPoint<HFq2> pi_b = HG2::add(HG2::add(b2, HG2::from_affine(zk->beta2)), HG2::mul(HG2::from_affine(zk->delta2), s));
-    HPoint<HFq> pb1 = HG1::add(HG1::add(b1, HG1::from_affine(zk->beta1)), HG1::mul(d1, s));
+    HPoint<HFq> pi_a = HG1::add(HG1::add(a, HG1::from_affine(zk->alpha1)), bl.rd1);
+    HPoint<HFq> pb1 = HG1::add(HG1::add(b1, HG1::from_affine(zk->beta1)), bl.sd1);
+    auto fsa = std::async(std::launch::async, [&] { return HG1::mul(pi_a, bl.s); });
+    auto fb = std::async(std::launch::async, [&] {
+        return HG2::to_affine(HG2::add(HG2::add(b2, HG2::from_affine(zk->beta2)), bl.sd2));
+    });
+    HPoint<HFq> rb1 = HG1::mul(pb1, bl.r);
     HPoint<HFq> pi_c = HG1::add(c, h);
-    pi_c = HG1::add(pi_c, HG1::mul(pi_a, s));
-    pi_c = HG1::add(pi_c, HG1::mul(pb1, r));
-    pi_c = HG1::add(pi_c, HG1::neg(HG1::mul(d1, rs)));
-    proof = proof_json(HG1::to_affine(pi_a), HG2::to_affine(pi_b), HG1::to_affine(pi_c), o.style);
+    pi_c = HG1::add(pi_c, fsa.get());
+    pi_c = HG1::add(pi_c, rb1);
+    pi_c = HG1::add(pi_c, HG1::neg(bl.rsd1));
+    HAffine<HFq> A = HG1::to_affine(pi_a), Cc = HG1::to_affine(pi_c);
+    proof = proof_json(A, fb.get(), Cc, o.style);
     pub = public_json(zk->public_bytes, o.style);
     zk->t_ms[9] = zk->t_horner_ms + std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -728,7 +787,7 @@ int g16_prove_combine(g16_zkey* zk, const uint8_t* partials, int count, char* pr
         if (opts) o = *opts;
         else g16_opts_default(&o);
         std::string proof, pub;
-        combine(zk, partials, count, o, proof, pub);
+        combine(zk, partials, count, o, make_blind(zk, o), proof, pub);
         return emit(proof, pub, proof_json, proof_len, public_json, public_len);
     });
 }
@@ -743,10 +802,11 @@ int g16_prove_loaded(g16_zkey* zk, char* proof_json, size_t* proof_len, char* pu
         if (opts) o = *opts;
         else g16_opts_default(&o);
         uint8_t partial[G16_PARTIAL_BYTES];
+        auto blind = std::async(std::launch::async, [&] { return make_blind(zk, o); });  // overlaps the GPU work
         prove_device(zk);
         export_partial(zk, partial);
         std::string proof, pub;
-        combine(zk, partial, 1, o, proof, pub);
+        combine(zk, partial, 1, o, blind.get(), proof, pub);
         return emit(proof, pub, proof_json, proof_len, public_json, public_len);
     });
 }
@@ -770,10 +830,11 @@ int g16_prove_files(const char* zkey_path, const char* wtns_path, const char* pr
         std::unique_ptr<g16_zkey> zk(zkey_build(fz.p, fz.len, &o));
         witness_load(zk.get(), fw.p, fw.len);
         uint8_t partial[G16_PARTIAL_BYTES];
+        auto blind = std::async(std::launch::async, [&] { return make_blind(zk.get(), o); });
         prove_device(zk.get());
         export_partial(zk.get(), partial);
         std::string proof, pub;
-        combine(zk.get(), partial, 1, o, proof, pub);
+        combine(zk.get(), partial, 1, o, blind.get(), proof, pub);
         write_file(proof_path, proof);
         write_file(public_path, pub);
         return (int)G16_OK;
@@ -820,6 +881,17 @@ int g16_last_accumulate_ms(const g16_zkey* zk, double out[5]) {
     out[2] = zk->B2.msm.accumulate_ms();
     out[3] = zk->C.msm.accumulate_ms();
     out[4] = zk->H.msm.accumulate_ms();
+    return G16_OK;
+}
+
+int g16_last_trace(const g16_zkey* zk, double out[30]) {
+    if (!zk || !out) return fail(G16_ERR_GENERIC, "null argument");
+    float t[6];
+    auto put = [&](int i, const auto& msm) {
+        msm.trace(zk->ev[0], t);
+        for (int k = 0; k < 6; k++) out[6 * i + k] = t[k];
+    };
+    put(0, zk->A.msm); put(1, zk->B1.msm); put(2, zk->B2.msm); put(3, zk->C.msm); put(4, zk->H.msm);
     return G16_OK;
 }
 
