@@ -179,7 +179,11 @@ def run_b200(args):
     zkey, wtns = fixture(args.workload, rank)
 
     t_open = time.perf_counter()
-    zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c)
+    shard = args.mode == "shard" and world > 1
+    if shard:
+        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, shard_rank=rank, shard_count=world)
+    else:
+        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c)
     t_open = time.perf_counter() - t_open
     zkey_len = len(zkey)
     del zkey
@@ -199,10 +203,24 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # sharded mode: ONE proof over all ranks (base-range shards of sections 5-9, the H pipeline replicated, one
+    # NCCL all-gather of 768-byte partials, every rank finalises); pinned r,s so all ranks agree
+    R_PIN, S_PIN = 0x1234567 << 200, 0x7654321 << 190
+
+    def step_loaded():
+        if shard:
+            return zk.combine(pkg.all_gather_partials(zk.prove_partial()), r=R_PIN, s=S_PIN)
+        return zk.prove_loaded()
+
+    def step_e2e():
+        if shard:
+            return pkg.prove_sharded(zk, pinned, r=R_PIN, s=S_PIN)
+        return zk.prove(pinned)
+
     # ---- resident arm: witness in HBM before the timed region -----------------------------------------------------
     zk.load_witness(pinned)
     for _ in range(args.warmup):
-        proof, public = zk.prove_loaded()
+        proof, public = step_loaded()
     clocks = ClockSampler(local)
     phase = {}
     acc_ms = {k: 0.0 for k in ("A", "B1", "B2", "C", "H")}
@@ -214,7 +232,7 @@ def run_b200(args):
     e0.record()
     w0 = time.perf_counter()
     for _ in range(args.steps):
-        proof, public = zk.prove_loaded()
+        proof, public = step_loaded()
         for k, v in zk.timings().items():
             phase[k] = phase.get(k, 0.0) + v
         for k, v in zk.accumulate_ms().items():
@@ -230,11 +248,11 @@ def run_b200(args):
 
     # ---- end-to-end arm: pinned host bytes in, JSON texts out, every step ------------------------------------------
     for _ in range(max(1, args.warmup // 2)):
-        zk.prove(pinned)
+        step_e2e()
     sync_all()
     w0 = time.perf_counter()
     for _ in range(args.steps):
-        proof, public = zk.prove(pinned)
+        proof, public = step_e2e()
     torch.cuda.synchronize(dev)
     e2e_s = max_over_ranks(time.perf_counter() - w0)
     d2h = len(proof) + len(public)
@@ -247,6 +265,7 @@ def run_b200(args):
             ok = bool(V.verify(json.load(f), json.loads(public), json.loads(proof)))
 
     steps = args.steps
+    jobs = 1 if shard else world     # proofs finished per step over the whole job
     g1_adds = sum(stats[k]["additions"] for k in ("A", "B1", "C", "H"))
     g2_adds = stats["B2"]["additions"]
     msm_points = 3 * nv - npub - 1 + zk.domain_size + nv
@@ -261,13 +280,14 @@ def run_b200(args):
         hbm_peak = peaks.get("hbm_gbs")
         ntt_gbs = NTT_BYTES_PER_POINT * zk.domain_size / (phase["ntt_pipeline"] / steps * 1e-3) / 1e9
         out = {
-            "metric": "groth16_prove_constraints_per_s", "value": ncons * steps * world / resident_s,
+            "metric": "groth16_prove_constraints_per_s", "value": ncons * steps * jobs / resident_s,
             "unit": "constraints/s", "n_gpus": world, "steps": steps, "warmup": args.warmup,
-            "ms_per_step": resident_s / steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": resident_s / steps * 1e3, "higher_is_better": True, "scaling": "strong" if shard else "weak",
             "vs_baseline": None, "dtype": "u32 limbs (256-bit Montgomery Fr/Fq/Fq2)", "data": "synthetic",
             "config": {"workload": args.workload, "description": desc, "n_vars": nv, "n_public": npub,
                        "n_constraints": ncons, "domain_size": zk.domain_size, "n_coefs": zk.n_coefs,
-                       "zkey_bytes": zkey_len, "proofs_per_step_per_gpu": 1, "parallelism": "replica-per-gpu",
+                       "zkey_bytes": zkey_len, "proofs_per_step": jobs,
+                       "parallelism": ("base-range shards x%d, NCCL all-gather of 768 B partials" % world) if shard else "replica-per-gpu",
                        "l2": "inputs exceed L2 (bases + scalars > 1 GB touched per step); no flush",
                        "timing": "cuda events on the default stream around synchronous prove calls, max(event, host clock), max over ranks"},
             "prove_s": resident_s / steps,
@@ -277,7 +297,7 @@ def run_b200(args):
             "trace_last_step_ms": zk.trace(),
             "zkey_open_s": t_open,
             "clocks": clk,
-            "e2e": {"value": ncons * steps * world / e2e_s, "unit": "constraints/s", "ms_per_step": e2e_s / steps * 1e3,
+            "e2e": {"value": ncons * steps * jobs / e2e_s, "unit": "constraints/s", "ms_per_step": e2e_s / steps * 1e3,
                     "h2d_bytes_per_step": len(wtns), "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "msm_accumulate_kernel (bucket accumulation, all five MSMs of a step)",
@@ -380,6 +400,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--mode", default="replica", choices=["replica", "shard"],
+                    help="N > 1: replica = one independent proof per GPU (weak scaling, default); shard = one proof "
+                         "over all GPUs, sections 5-9 split by base range, one all-gather of partial sums (strong scaling)")
     ap.add_argument("--msm-c", type=int, default=0, help="Pippenger window bits (0 = automatic)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", dest="verify", action="store_false")
