@@ -5,7 +5,7 @@ NVCC     ?= nvcc
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
 OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o
-HDRS     := $(wildcard $(CSRC)/*.cuh) $(wildcard $(CSRC)/*.hpp) include/g16_b200.h
+HDRS     := $(wildcard $(CSRC)/*.cuh) $(filter-out $(CSRC)/service%,$(wildcard $(CSRC)/*.hpp)) include/g16_b200.h
 
 all: $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover
 
@@ -18,8 +18,8 @@ $(PKG)/libg16b200.so: $(OBJS)
 $(PKG)/libg16synth.so: $(CSRC)/synth.o
 	$(NVCC) $(ARCH) -shared -o $@ $< -lcudart
 
-$(PKG)/prover: $(CSRC)/prover_main.cpp include/g16_b200.h $(PKG)/libg16b200.so
-	g++ -O2 -std=c++17 -Iinclude $< -o $@ -L$(PKG) -lg16b200 -Wl,-rpath,'$$ORIGIN'
+$(PKG)/prover: $(CSRC)/prover_main.cpp $(wildcard $(CSRC)/service*.hpp) include/g16_b200.h $(PKG)/libg16b200.so
+	g++ -O2 -std=c++17 -Wall -Iinclude $< -o $@ -L$(PKG) -lg16b200 -lpthread -Wl,-rpath,'$$ORIGIN'
 
 clean:
 	rm -f $(CSRC)/*.o $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover

@@ -140,6 +140,15 @@ G2_MADD_MODMULS = 28      # the same over Fq2: 8 x 3 (Karatsuba) + 2 x 2
 NTT_BYTES_PER_POINT = 384  # H pipeline, strict: 6 transforms x (32 B read + 32 B write) per domain point
 
 
+def measured_traffic(workload):
+    """dram bytes from the committed ncu --set full capture of this workload (profiles/traffic.json), or {}"""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(workload, {})
+    except (OSError, ValueError):
+        return {}
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -275,6 +284,8 @@ def run_b200(args):
     out = None
     if rank == 0:
         peaks = measured_peaks()
+        traffic = measured_traffic(args.workload)
+        acc_alg_bytes = 68 * g1_adds + 132 * g2_adds      # one base record + one 4-byte entry per mixed addition
         imad_peak = pkg.bench_int_pipe(1)            # wide multiply-adds per second, measured on this GPU now
         modmul_peak = pkg.bench_int_pipe(2)          # dependent-chain Montgomery products per second
         hbm_peak = peaks.get("hbm_gbs")
@@ -307,10 +318,14 @@ def run_b200(args):
                          "peak_source": "g16_bench_int_pipe(1): IMAD.WIDE.U32 carry chains, measured in this run "
                                         "(MEASURED_PEAKS.json has no integer figure)",
                          "modmul_peak_per_s": modmul_peak, "share_of_step": acc_total_ms / (resident_s / steps * 1e3),
-                         "traffic": None},
+                         "algorithmic_bytes": acc_alg_bytes,
+                         "traffic": traffic.get("msm_accumulate", {}).get("bytes_per_step"),
+                         "traffic_source": traffic.get("msm_accumulate", {}).get("source")},
             "roofline_ntt": {"kernel": "ntt_pass_kernel x passes + r1cs/join (H pipeline)", "bound": "hbm",
                              "achieved": ntt_gbs, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": ntt_gbs / hbm_peak if hbm_peak else None, "traffic": None,
+                             "frac": ntt_gbs / hbm_peak if hbm_peak else None,
+                             "traffic": (traffic["ntt_pass"]["bytes_per_launch"] * traffic["ntt_pass"]["launches_per_step"])
+                             if "ntt_pass" in traffic else None,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "unavailable"},
             "verified": ok,
         }

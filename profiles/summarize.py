@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Turn ncu outputs under gpurun_out/ into the small text summaries committed under profiles/.
-usage: summarize.py launches <launches.csv> <proves in the run>   |   summarize.py raw <report.ncu-rep>"""
+usage: summarize.py launches <launches.csv> <proves in the run>   |   summarize.py raw <report.ncu-rep | raw-page.csv>"""
 import collections, csv, re, subprocess, sys
 
 def launches(path, proves):
@@ -19,7 +19,10 @@ def launches(path, proves):
         print("%s | %d | %.0f | %.0f | %.1f%%" % (k, c, v, v / proves, 100 * v / tot))
 
 def raw(path):
-    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    if path.endswith(".csv"):   # already exported on the GPU box: ncu -i x.ncu-rep --page raw --csv
+        out = open(path).read()
+    else:
+        out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     hdr, units = rows[0], rows[1]
     want = ["Kernel Name", "launch__grid_size", "launch__registers_per_thread", "gpu__time_duration.sum",
@@ -29,6 +32,8 @@ def raw(path):
             "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
             "smsp__pcsamp_warps_issue_stalled_math_pipe_throttle", "smsp__pcsamp_warps_issue_stalled_wait",
             "smsp__pcsamp_warps_issue_stalled_no_instructions", "smsp__pcsamp_warps_issue_stalled_long_scoreboard",
+            "smsp__pcsamp_warps_issue_stalled_barrier", "smsp__pcsamp_warps_issue_stalled_short_scoreboard",
+            "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
             "smsp__pcsamp_warps_issue_stalled_not_selected", "smsp__pcsamp_warps_issue_stalled_selected"]
     idx = {h: i for i, h in enumerate(hdr)}
     for r in rows[2:]:

@@ -258,40 +258,76 @@ msm_combine2_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __res
     if (threadIdx.x == 0) buckets[k] = acc;
 }
 
-// thread per chunk of L buckets of one window: out = sum_{b in chunk} (b+1) * B_b
-template <class C>
+// Bucket reduction, sum_b (b+1) B_b per window, in two levels so that no thread multiplies by its chunk offset at
+// the bucket level (that double-and-add was a third of the kernel):  with chunks of L,
+//   sum_b (b+1) B_b = sum_ch A0_ch + L * sum_ch ch * S0_ch,   A0_ch = sum_j (j+1) B_{L ch + j},  S0_ch = sum_j B_{L ch + j}
+// and the second sum is the same problem over the cpw = bpw/L chunk sums (zero-based weights), where the offset
+// multiplication is paid once per L*L buckets.
+// Thread per chunk of L consecutive points of one window:
+//   A_out[t] = sum_j (j + ONE_BASED) X[lo + j]  (+ lo * sum_j X[lo + j]  if MUL);   S_out[t] = sum_j X[lo + j] (if given)
+template <class C, bool ONE_BASED, bool MUL>
 __global__ void __launch_bounds__(64)
-msm_chunk_reduce_kernel(const typename C::pt* __restrict__ buckets, uint32_t buckets_per_window, uint32_t L,
-                        uint32_t chunks_per_window, uint32_t nchunks, typename C::pt* __restrict__ chunk_out) {
+msm_chunk_reduce_kernel(const typename C::pt* __restrict__ in, uint32_t per_window, uint32_t L,
+                        uint32_t chunks_per_window, uint32_t nchunks, typename C::pt* __restrict__ A_out,
+                        typename C::pt* __restrict__ S_out) {
     typedef typename C::pt pt;
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= nchunks) return;
     uint32_t w = t / chunks_per_window, ch = t % chunks_per_window;
     uint32_t lo = ch * L;
-    uint32_t hi = min(lo + L, buckets_per_window);
-    const pt* B = buckets + size_t(w) * buckets_per_window;
+    uint32_t hi = min(lo + L, per_window);
+    const pt* X = in + size_t(w) * per_window;
     pt run = C::identity(), acc = C::identity();
     for (uint32_t b = hi; b-- > lo;) {
-        C::add(run, B[b]);
-        C::add(acc, run);
+        if (ONE_BASED) {
+            C::add(run, X[b]);
+            C::add(acc, run);
+        } else {
+            C::add(acc, run);
+            C::add(run, X[b]);
+        }
     }
-    if (lo) {
+    if (MUL && lo) {
         pt s = C::mul_small(run, lo);
         C::add(acc, s);
     }
-    chunk_out[t] = acc;
+    A_out[t] = acc;
+    if (S_out) S_out[t] = run;
 }
 
-// one CTA per window: tree-sum its chunk results
+// CTA (w, p) sums slice p of window w's `per_window` points: out[w * slices + p]
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-msm_window_sum_kernel(const typename C::pt* __restrict__ chunk_out, uint32_t chunks_per_window,
-                      typename C::pt* __restrict__ window_out) {
-    const typename C::pt* p = chunk_out + size_t(blockIdx.x) * chunks_per_window;
+msm_sum_slices_kernel(const typename C::pt* __restrict__ in, uint32_t per_window, uint32_t slices,
+                      typename C::pt* __restrict__ out) {
+    uint32_t w = blockIdx.x / slices, p = blockIdx.x % slices;
+    uint32_t len = (per_window + slices - 1) / slices;
+    uint32_t lo = p * len, hi = min(lo + len, per_window);
+    const typename C::pt* X = in + size_t(w) * per_window;
     typename C::pt acc = C::identity();
-    for (uint32_t i = threadIdx.x; i < chunks_per_window; i += THREADS) C::add(acc, p[i]);
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += THREADS) C::add(acc, X[i]);
     block_sum_points<C, THREADS>(acc);
-    if (threadIdx.x == 0) window_out[blockIdx.x] = acc;
+    if (threadIdx.x == 0) out[blockIdx.x] = acc;
+}
+
+// one CTA per window: window sum = sum of a0[n0] + L * sum of a1[n1]
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+msm_window_sum_kernel(const typename C::pt* __restrict__ a0, uint32_t n0, const typename C::pt* __restrict__ a1,
+                      uint32_t n1, uint32_t L, typename C::pt* __restrict__ window_out) {
+    const typename C::pt* p = a0 + size_t(blockIdx.x) * n0;
+    const typename C::pt* q = a1 + size_t(blockIdx.x) * n1;
+    typename C::pt acc = C::identity(), hi = C::identity();
+    for (uint32_t i = threadIdx.x; i < n0; i += THREADS) C::add(acc, p[i]);
+    for (uint32_t i = threadIdx.x; i < n1; i += THREADS) C::add(hi, q[i]);
+    block_sum_points<C, THREADS>(acc);
+    __syncthreads();
+    block_sum_points<C, THREADS>(hi);
+    if (threadIdx.x == 0) {
+        typename C::pt s = C::mul_small(hi, L);
+        C::add(acc, s);
+        window_out[blockIdx.x] = acc;
+    }
 }
 
 // bit i of mask = base i is the all-zero record (infinity)
@@ -372,7 +408,11 @@ public:
         task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
         cut_list.alloc((m_max / T_MIN + 2) * 4);  // a cut bucket holds more than T >= T_MIN entries
         buckets.alloc(size_t(nb) * sizeof(pt));
+        cpw1 = (cpw + L - 1) / L;
         chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
+        chunk_sum.alloc(size_t(W) * cpw * sizeof(pt));
+        chunk2_out.alloc(size_t(W) * cpw1 * sizeof(pt));
+        slice_out.alloc(size_t(W) * SUM_SLICES * sizeof(pt));
         window_out.alloc(size_t(W) * sizeof(pt));
         counters.alloc(64);
         size_t t1 = 0, t3 = 0;
@@ -477,11 +517,15 @@ public:
         G16_CUDA(cudaEventRecord(ev_t[2], s));
     }
 
-    // stage 3: accumulate + reductions (reads the task count -> one stream sync); window sums go to the host
-    void stage3() {
-        cudaStream_t s = stream;
+    // stage 3: accumulate + reductions (reads the task count -> one stream sync); window sums go to the host.
+    // `s3` (optional) = a different stream for this stage: the prover keeps the H MSM's digits + sort on the
+    // high-priority transform stream (so the sort is not starved by the witness MSMs' accumulations) and its
+    // accumulation on the lowest-priority stream (so it fills the machine under everything else).
+    void stage3(cudaStream_t s3 = nullptr) {
+        cudaStream_t s = s3 ? s3 : stream;
+        if (s != stream) G16_CUDA(cudaStreamWaitEvent(s, ev_t[2], 0));
         if (m != 0) {
-            G16_CUDA(cudaStreamSynchronize(s));
+            G16_CUDA(cudaStreamSynchronize(stream));
             const uint32_t* h32 = reinterpret_cast<const uint32_t*>(h_counters);
             uint32_t nt = h32[4], np = h32[5], nblocks = h32[6], ncut = h32[7];
             stats.tasks = nt;
@@ -526,14 +570,27 @@ public:
                 G16_CUDA(cudaGetLastError());
             }
         }
-        uint32_t nchunks = uint32_t(W) * cpw;
-        msm_chunk_reduce_kernel<C><<<(nchunks + 63) / 64, 64, 0, s>>>(buckets.as<pt>(), bpw, L, cpw, nchunks,
-                                                                      chunk_out.as<pt>());
-        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(chunk_out.as<pt>(), cpw, window_out.as<pt>());
+        uint32_t nchunks = uint32_t(W) * cpw, nchunks1 = uint32_t(W) * cpw1;
+        msm_chunk_reduce_kernel<C, true, false><<<(nchunks + 63) / 64, 64, 0, s>>>(
+            buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
+        msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
+            chunk_sum.as<pt>(), cpw, L, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
+        const pt* a0 = chunk_out.as<pt>();
+        uint32_t n0 = cpw;
+        if (cpw >= 32 * SUM_SLICES) {  // long windows: sum the level-0 results in slices first (short dependency chains)
+            msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * SUM_SLICES, RED_THREADS, 0, s>>>(
+                chunk_out.as<pt>(), cpw, SUM_SLICES, slice_out.as<pt>());
+            a0 = slice_out.as<pt>();
+            n0 = SUM_SLICES;
+            G16_LAUNCHED(1);
+        }
+        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(a0, n0, chunk2_out.as<pt>(), cpw1, L,
+                                                                        window_out.as<pt>());
         G16_CUDA(cudaGetLastError());
-        G16_LAUNCHED(2);
+        G16_LAUNCHED(3);
         G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));
         G16_CUDA(cudaEventRecord(ev_t[3], s));
+        stream = s;
     }
 
     // whole MSM on one stream; returns after the window sums are in host memory
@@ -566,6 +623,7 @@ public:
 
 private:
     static constexpr int RED_THREADS = 128;
+    static constexpr uint32_t SUM_SLICES = 32;
     static void grow(DevBuf& b, size_t bytes) {
         if (bytes > b.bytes) b.alloc(bytes + bytes / 4 + 4096);
     }
@@ -576,12 +634,13 @@ private:
     }
     MsmConfig cfg;
     size_t cap_n = 0, n = 0, m = 0, slots = 148 * 1024;
-    uint32_t bpw = 0, nb = 0, cpw = 0;
+    uint32_t bpw = 0, nb = 0, cpw = 0, cpw1 = 0;
     const aff* bases = nullptr;
     cudaStream_t stream = 0;
     uint32_t *sorted_keys = nullptr, *sorted_vals = nullptr;
     DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
-        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, chunk_out, window_out, counters, cub_tmp,
+        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, chunk_out, chunk_sum, chunk2_out, slice_out,
+        window_out, counters, cub_tmp,
         task_tmp;
     unsigned long long* h_counters = nullptr;
     pt* h_windows = nullptr;

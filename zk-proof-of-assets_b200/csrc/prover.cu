@@ -170,6 +170,7 @@ struct g16_zkey {
     DevBuf pa, pb, pc;         // A, B, C evaluations; pa ends up holding the H scalars
     NttDomain dom;
     cudaStream_t s_main = nullptr, s_msm[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaStream_t s_pre[4] = {nullptr, nullptr, nullptr, nullptr};  // witness MSMs: digits + sort (high priority)
     cudaEvent_t ev[16];
     bool ev_ok = false;
     bool witness_loaded = false;
@@ -181,6 +182,8 @@ struct g16_zkey {
     ~g16_zkey() {
         cudaSetDevice(device);
         if (s_main) cudaStreamDestroy(s_main);
+        for (auto& s : s_pre)
+            if (s) cudaStreamDestroy(s);
         for (auto& s : s_msm)
             if (s) cudaStreamDestroy(s);
         if (ev_ok)
@@ -287,6 +290,9 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     G16_CUDA(cudaStreamCreateWithPriority(&zk->s_main, cudaStreamNonBlocking, prio_hi));
     for (int i = 0; i < 5; i++)
         G16_CUDA(cudaStreamCreateWithPriority(&zk->s_msm[i], cudaStreamNonBlocking, i == 4 ? prio_lo : prio_mid));
+    // digits + sort of the witness MSMs are HBM-bound and short; at the transforms' priority they interleave with the
+    // (integer-bound) transforms instead of being starved by them, so the accumulations are ready when the transforms end
+    for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamCreateWithPriority(&zk->s_pre[i], cudaStreamNonBlocking, prio_hi));
     for (auto& e : zk->ev) G16_CUDA(cudaEventCreate(&e));
     zk->ev_ok = true;
     Msm<G1>::prepare();
@@ -500,19 +506,20 @@ static void prove_device(g16_zkey* zk) {
     G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
     // witness-scalar MSMs start at once; the H MSM waits for the NTT pipeline
     for (int i = 0; i < 4; i++) {
-        G16_CUDA(cudaStreamWaitEvent(zk->s_msm[i], zk->ev[0], 0));
-        G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_msm[i]));
+        G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], zk->ev[0], 0));
+        G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_pre[i]));
     }
-    zk->A.msm.stage1(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_msm[0]);
-    zk->B1.msm.stage1(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_msm[1]);
-    zk->B2.msm.stage1(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_msm[2]);
+    zk->A.msm.stage1(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_pre[0]);
+    zk->B1.msm.stage1(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_pre[1]);
+    zk->B2.msm.stage1(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2]);
     zk->C.msm.stage1(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8,
-                     zk->C.mask.as<uint32_t>(), zk->C.n, zk->s_msm[3]);
+                     zk->C.mask.as<uint32_t>(), zk->C.n, zk->s_pre[3]);
     enqueue_h_pipeline(zk);
-    G16_CUDA(cudaStreamWaitEvent(zk->s_msm[4], zk->ev[2], 0));
-    G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_msm[4]));
+    // H digits + sort stay on the transform stream (highest priority, already ordered after the join); only the
+    // accumulation and reductions move to the lowest-priority stream (Msm::stage3)
+    G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
     zk->H.msm.stage1(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
-                     zk->s_msm[4]);
+                     zk->s_main);
     // Each MSM has two points where the host must read a counter back (entry count, task count).  One host thread
     // per MSM drives those, so a wait on one stream never delays the launches of another (the H chain in particular
     // must be enqueued the moment the transforms finish).
@@ -520,7 +527,7 @@ static void prove_device(g16_zkey* zk) {
     auto drive = [dev](auto* msm, cudaStream_t st, cudaEvent_t done) {
         G16_CUDA(cudaSetDevice(dev));
         msm->stage2();
-        msm->stage3();
+        msm->stage3(st);
         G16_CUDA(cudaEventRecord(done, st));
         G16_CUDA(cudaStreamSynchronize(st));
     };

@@ -5,30 +5,74 @@
 // (scripts/lib/error_handling.sh:16-41).  Optional environment knobs never change the argv contract:
 //   G16_DEVICE=<ordinal>   G16_STYLE=snarkjs|rapidsnark   G16_MSM_C=<bits>   G16_VERBOSE=1
 //   G16_R=<decimal> G16_S=<decimal>   pin the blinding factors (test hook)
+//   G16_SERVICE=<socket path>          send the request to a resident-key service (below) instead of proving in process
+// Service mode (not part of the reference's contract, see csrc/service.hpp):
+//     prover --serve [--socket PATH] [--devices 0,1,...] [--max-keys N]
+//     prover --ping | --stats | --shutdown          (socket from --socket or G16_SERVICE)
+#include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
 
 #include "g16_b200.h"
+#include "service_handlers.hpp"
 
-static bool dec_to_le32(const char* s, uint8_t out[32]) {
-    std::memset(out, 0, 32);
-    if (!*s) return false;
-    for (; *s; s++) {
-        if (*s < '0' || *s > '9') return false;
-        unsigned carry = unsigned(*s - '0');
-        for (int i = 0; i < 32; i++) {
-            unsigned v = out[i] * 10u + carry;
-            out[i] = uint8_t(v);
-            carry = v >> 8;
+static const char* DEFAULT_SOCKET = "/tmp/g16b200.sock";
+
+static std::string absolute(const char* p, bool must_exist) {
+    char real[PATH_MAX];
+    if (must_exist && ::realpath(p, real)) return real;
+    if (p[0] == '/') return p;
+    if (!::getcwd(real, sizeof real)) return p;
+    return std::string(real) + "/" + p;
+}
+
+static int control(int argc, char** argv) {
+    std::string sock = std::getenv("G16_SERVICE") ? std::getenv("G16_SERVICE") : DEFAULT_SOCKET;
+    std::string devs;
+    int max_keys = 4;
+    std::string cmd = argv[1];
+    for (int i = 2; i < argc; i++) {
+        std::string a = argv[i];
+        if (a == "--socket" && i + 1 < argc) sock = argv[++i];
+        else if (a == "--devices" && i + 1 < argc) devs = argv[++i];
+        else if (a == "--max-keys" && i + 1 < argc) max_keys = std::atoi(argv[++i]);
+        else {
+            std::fprintf(stderr, "prover: unknown option %s\n", a.c_str());
+            return 1;
         }
-        if (carry) return false;
     }
-    return true;
+    if (cmd == "--serve") {
+        std::vector<int> devices;
+        if (devs.empty()) {
+            if (const char* e = std::getenv("G16_DEVICE")) devs = e;
+            else devs = "0";
+        }
+        size_t pos = 0;
+        while (pos <= devs.size()) {
+            size_t q = devs.find(',', pos);
+            if (q == std::string::npos) q = devs.size();
+            if (q > pos) devices.push_back(std::atoi(devs.substr(pos, q - pos).c_str()));
+            pos = q + 1;
+        }
+        if (devices.empty()) devices.push_back(0);
+        return g16svc::Server(sock, devices, max_keys).run();
+    }
+    std::string reply;
+    std::string req = cmd == "--ping" ? "PING\n\n" : cmd == "--stats" ? "STATS\n\n" : "SHUTDOWN\n\n";
+    if (!g16svc::exchange(sock, req, reply)) {
+        std::fprintf(stderr, "prover: no service on %s\n", sock.c_str());
+        return 1;
+    }
+    std::fputs(reply.c_str(), stdout);
+    return reply.compare(0, 2, "OK") == 0 ? 0 : 1;
 }
 
 int main(int argc, char** argv) {
+    if (argc >= 2 && (!std::strcmp(argv[1], "--serve") || !std::strcmp(argv[1], "--ping") ||
+                      !std::strcmp(argv[1], "--stats") || !std::strcmp(argv[1], "--shutdown")))
+        return control(argc, argv);
     if (argc != 5) {
         std::fprintf(stderr, "Invalid number of parameters\nUsage: prover <circuit.zkey> <witness.wtns> <proof.json> <public.json>\n");
         return 1;
@@ -41,11 +85,33 @@ int main(int argc, char** argv) {
     const char* er = std::getenv("G16_R");
     const char* es = std::getenv("G16_S");
     if (er && es) {
-        if (!dec_to_le32(er, o.r) || !dec_to_le32(es, o.s)) {
+        if (!g16svc::dec_to_le32(er, o.r) || !g16svc::dec_to_le32(es, o.s)) {
             std::fprintf(stderr, "prover: G16_R / G16_S must be decimal integers below 2^256\n");
             return 1;
         }
         o.has_rs = 1;
+    }
+    if (const char* sock = std::getenv("G16_SERVICE")) {
+        std::string req = "PROVE\n" + absolute(argv[1], true) + "\n" + absolute(argv[2], true) + "\n" +
+                          absolute(argv[3], false) + "\n" + absolute(argv[4], false) + "\n" +
+                          (o.style == G16_STYLE_SNARKJS ? "1" : "0") + "\n" + (o.has_rs ? er : "-") + "\n" +
+                          (o.has_rs ? es : "-") + "\n\n";
+        std::string reply;
+        if (g16svc::exchange(sock, req, reply)) {
+            if (reply.compare(0, 2, "OK") == 0) {
+                if (std::getenv("G16_VERBOSE")) std::fprintf(stderr, "prover: service %s", reply.c_str());
+                return 0;
+            }
+            // "ERR <code> <message>"
+            int code = 1;
+            size_t sp = reply.find(' ', 4);
+            if (reply.size() > 4) code = std::atoi(reply.c_str() + 4);
+            std::string msg = sp == std::string::npos ? reply : reply.substr(sp + 1);
+            while (!msg.empty() && msg.back() == '\n') msg.pop_back();
+            std::fprintf(stderr, "prover: %s\n", msg.c_str());
+            return code ? code : 1;
+        }
+        std::fprintf(stderr, "prover: no service on %s, proving in process\n", sock);
     }
     int rc = g16_prove_files(argv[1], argv[2], argv[3], argv[4], &o);
     if (rc != G16_OK) {
