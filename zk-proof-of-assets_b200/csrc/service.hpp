@@ -11,6 +11,8 @@
 //   PING | STATS | SHUTDOWN
 // Reply: "OK <text>\n" or "ERR <g16_status> <message>\n".  Paths must be absolute (the client resolves them).
 #pragma once
+#include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/socket.h>
 #include <sys/stat.h>
 #include <sys/un.h>
@@ -62,6 +64,37 @@ inline bool read_file(const std::string& path, std::vector<uint8_t>& out, std::s
     if (got != out.size()) { err = "short read on " + path; return false; }
     return true;
 }
+
+// read-only mapping of a whole file (the witness: up to 1.7 GB, copied once, by the H2D transfer itself)
+struct Mapped {
+    const uint8_t* p = nullptr;
+    size_t n = 0;
+    ~Mapped() {
+        if (p && n) ::munmap(const_cast<uint8_t*>(p), n);
+    }
+    bool open(const std::string& path, std::string& err) {
+        int fd = ::open(path.c_str(), O_RDONLY);
+        struct stat st;
+        if (fd < 0 || ::fstat(fd, &st) != 0) {
+            err = "cannot open " + path + ": " + std::strerror(errno);
+            if (fd >= 0) ::close(fd);
+            return false;
+        }
+        n = size_t(st.st_size);
+        if (n) {
+            void* m = ::mmap(nullptr, n, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
+            if (m == MAP_FAILED) {
+                err = "cannot map " + path + ": " + std::strerror(errno);
+                ::close(fd);
+                n = 0;
+                return false;
+            }
+            p = static_cast<const uint8_t*>(m);
+        }
+        ::close(fd);
+        return true;
+    }
+};
 
 // write to a temporary beside the target, then rename: a reader never sees a half-written proof
 inline bool write_file(const std::string& path, const char* data, size_t n, std::string& err) {

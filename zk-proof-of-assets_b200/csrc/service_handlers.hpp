@@ -28,8 +28,8 @@ inline std::string Server::prove(const std::vector<std::string>& f) {
             return err_reply(G16_ERR_GENERIC, "r / s must be decimal integers below 2^256");
         o.has_rs = 1;
     }
-    std::vector<uint8_t> wtns;
-    if (!read_file(f[2], wtns, err)) return err_reply(G16_ERR_GENERIC, err);
+    Mapped wtns;
+    if (!wtns.open(f[2], err)) return err_reply(G16_ERR_GENERIC, err);
 
     bool must_open = false;
     std::shared_ptr<Resident> r = acquire(key, must_open);
@@ -56,7 +56,7 @@ inline std::string Server::prove(const std::vector<std::string>& f) {
     std::vector<char> proof(4096), pub(256 + 80 * size_t(npub));
     size_t pl = proof.size(), ul = pub.size();
     auto tp = std::chrono::steady_clock::now();
-    int rc = g16_prove(r->zk, wtns.data(), wtns.size(), proof.data(), &pl, pub.data(), &ul, &o);
+    int rc = g16_prove(r->zk, wtns.p, wtns.n, proof.data(), &pl, pub.data(), &ul, &o);
     double prove_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp).count();
     std::string msg = rc == G16_OK ? "" : g16_last_error();
     int device = r->device;
