@@ -11,6 +11,7 @@ constraints/s per layer"); `ms_per_step` is the prove time, `msm_mpts_per_s` the
   e2e   : the public call ZKey.prove(wtns bytes in pinned host memory) -> JSON texts in host memory, per step
 N > 1   : one process per GPU, every rank proves its own independent batch proof (the reference's GNU-parallel batch
           loop, scripts/full_workflow.sh:552): weak scaling, no data-path collective; barrier + max over ranks.
+          --mode shard: ONE proof over all ranks instead (strong scaling; NCCL for slices and 768-byte partials).
 Inputs are synthetic (SYNTH-1 circuits shaped like the reference's layers, known-trapdoor setup): the reference commits
 no .zkey/.wtns and none can be generated offline.  The reference arm (--impl reference) times the CPU oracle port
 (oracle/c/oracle.c, all host threads) because neither rapidsnark nor snarkjs can be installed here.
@@ -188,7 +189,8 @@ def run_b200(args):
     zkey, wtns = fixture(args.workload, rank)
 
     t_open = time.perf_counter()
-    shard = args.mode == "shard" and world > 1
+    shard = args.mode in ("shard", "shard-rep") and world > 1
+    dist_ntt = args.mode == "shard"     # coset transforms spread over the ranks too (one all-to-all per polynomial)
     if shard:
         zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, shard_rank=rank, shard_count=world)
     else:
@@ -217,11 +219,15 @@ def run_b200(args):
     R_PIN, S_PIN = 0x1234567 << 200, 0x7654321 << 190
 
     def step_loaded():
+        if shard and dist_ntt:
+            return pkg.prove_sharded_distributed(zk, None, r=R_PIN, s=S_PIN)
         if shard:
             return zk.combine(pkg.all_gather_partials(zk.prove_partial()), r=R_PIN, s=S_PIN)
         return zk.prove_loaded()
 
     def step_e2e():
+        if shard and dist_ntt:
+            return pkg.prove_sharded_distributed(zk, pinned, r=R_PIN, s=S_PIN)
         if shard:
             return pkg.prove_sharded(zk, pinned, r=R_PIN, s=S_PIN)
         return zk.prove(pinned)
@@ -298,7 +304,9 @@ def run_b200(args):
             "config": {"workload": args.workload, "description": desc, "n_vars": nv, "n_public": npub,
                        "n_constraints": ncons, "domain_size": zk.domain_size, "n_coefs": zk.n_coefs,
                        "zkey_bytes": zkey_len, "proofs_per_step": jobs,
-                       "parallelism": ("base-range shards x%d, NCCL all-gather of 768 B partials" % world) if shard else "replica-per-gpu",
+                       "parallelism": ("base-range shards x%d, %s, NCCL all-gather of 768 B partials"
+                                       % (world, "A/B/C transforms on ranks 0-%d + all-to-all of slices" % (min(world, 3) - 1)
+                                          if dist_ntt else "transforms replicated")) if shard else "replica-per-gpu",
                        "l2": "inputs exceed L2 (bases + scalars > 1 GB touched per step); no flush",
                        "timing": "cuda events on the default stream around synchronous prove calls, max(event, host clock), max over ranks"},
             "prove_s": resident_s / steps,
@@ -415,9 +423,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
-    ap.add_argument("--mode", default="replica", choices=["replica", "shard"],
+    ap.add_argument("--mode", default="replica", choices=["replica", "shard", "shard-rep"],
                     help="N > 1: replica = one independent proof per GPU (weak scaling, default); shard = one proof "
-                         "over all GPUs, sections 5-9 split by base range, one all-gather of partial sums (strong scaling)")
+                         "over all GPUs (strong scaling): sections 5-9 split by base range, the A/B/C coset transforms on "
+                         "ranks 0-2 with an all-to-all of their slices, one all-gather of partial sums; shard-rep = the "
+                         "same with the transforms repeated on every rank (no slice exchange)")
     ap.add_argument("--msm-c", type=int, default=0, help="Pippenger window bits (0 = automatic)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", dest="verify", action="store_false")

@@ -81,6 +81,17 @@ int g16_prove_partial(g16_zkey* zk, uint8_t* partial_out);
 int g16_prove_combine(g16_zkey* zk, const uint8_t* partials, int count, char* proof_json, size_t* proof_len,
                       char* public_json, size_t* public_len, const g16_opts* opts);
 
+/* Transforms spread over the ranks (SURVEY.md 8(e) task placement): with G >= 2 ranks the three coset transforms
+ * (rows a5-a7 for A, B, C) need not be repeated on every rank.  Rank o runs g16_h_transform(zk, mask of the
+ * polynomials it owns: 1 = A, 2 = B, 4 = C): R1CS evaluation (row a4, cheap, every rank) + the odd-coset transform of
+ * those polynomials, left in the handle's device buffers (domain_size x 32 B each, Montgomery).  The caller then moves
+ * each polynomial's slice [h_lo, h_lo + h_n) from its owner to every rank (one NCCL all-to-all per polynomial;
+ * g16_h_buffer gives the device pointers and this shard's H range) and calls g16_prove_partial_joined with device
+ * pointers to its three received slices (h_n x 32 B each): the join (row a8) runs on the range only. */
+int g16_h_transform(g16_zkey* zk, int which);
+int g16_h_buffer(g16_zkey* zk, int poly /*0 A, 1 B, 2 C*/, void** d_ptr, uint64_t* h_lo, uint64_t* h_n);
+int g16_prove_partial_joined(g16_zkey* zk, const void* d_a, const void* d_b, const void* d_c, uint8_t* partial_out);
+
 /* ---- operators on the path, usable on their own (metric: BN254 MSM Mpts/s; NTT GB/s) ------------------------
  * MSM: bases = zkey records (affine, Montgomery, all-zero = infinity; 64 B G1 / 128 B G2), scalars = 32 B standard
  * form.  *_host take host pointers (copies inside), *_dev take device pointers.  Result: affine, Montgomery,

@@ -366,13 +366,18 @@ zkey = open(sys.argv[2], "rb").read(); wtns = open(sys.argv[3], "rb").read()
 zk = pkg.ZKey(zkey, device=0, shard_rank=rank, shard_count=world)
 proof, public = pkg.prove_sharded(zk, wtns, r=424242, s=171717)
 open(sys.argv[4] + ".%d" % rank, "w").write(proof + "\n" + public)
+# same proof with the three coset transforms spread over the ranks and their slices exchanged
+p2, u2 = pkg.prove_sharded_distributed(zk, wtns, r=424242, s=171717)
+open(sys.argv[4] + ".dist.%d" % rank, "w").write(p2 + "\n" + u2)
 zk.close()
 dist.barrier(); dist.destroy_process_group()
 '''
 
 
-def test_prove_sharded_two_ranks(pkg, small_fixture, tmp_path):
-    """One proof over two ranks (base-range shards, 768-byte partial gather) == the whole-key proof, on every rank."""
+@pytest.mark.parametrize("world", [2, 3])
+def test_prove_sharded_ranks(pkg, small_fixture, tmp_path, world):
+    """One proof over several ranks (base-range shards, 768-byte partial gather; then also with the transforms
+    spread over the ranks and an all-to-all of their slices) == the whole-key proof, on every rank."""
     import socket
     import sys
     f = small_fixture
@@ -383,8 +388,8 @@ def test_prove_sharded_two_ranks(pkg, small_fixture, tmp_path):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     procs = []
-    for rank in range(2):
-        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    for rank in range(world):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
         procs.append(subprocess.Popen([sys.executable, str(tmp_path / "worker.py"), ROOT, str(tmp_path / "k.zkey"),
                                        str(tmp_path / "w.wtns"), str(tmp_path / "out")], env=env,
                                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
@@ -392,5 +397,6 @@ def test_prove_sharded_two_ranks(pkg, small_fixture, tmp_path):
         out = p.communicate(timeout=300)[0]
         assert p.returncode == 0, out
     want = "\n".join(g16.prove(f["zk"], f["w"], 424242, 171717))
-    for rank in range(2):
+    for rank in range(world):
         assert (tmp_path / ("out.%d" % rank)).read_text() == want
+        assert (tmp_path / ("out.dist.%d" % rank)).read_text() == want

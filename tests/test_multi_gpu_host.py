@@ -22,6 +22,16 @@ def test_shard_ranges_partition_every_section():
         pkg.shard_range(10, 2, 2)
 
 
+def test_transform_owners_cover_the_three_polynomials():
+    pkg = load_pkg()
+    for world in (1, 2, 3, 4, 8):
+        owners = [pkg.transform_owner(p, world) for p in range(3)]
+        assert all(0 <= o < world for o in owners)
+        assert len(set(owners)) == min(world, 3)          # spread over as many ranks as there are (at most three)
+        masks = [sum(1 << p for p in range(3) if owners[p] == g) for g in range(world)]
+        assert sum(masks) == 7 and all(m & k == 0 for i, m in enumerate(masks) for k in masks[i + 1:])
+
+
 WORKER = r'''
 import os, sys
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))

@@ -36,7 +36,8 @@ ABI_SYMBOLS = [
     "g16_prove_combine", "g16_msm_g1_host", "g16_msm_g2_host", "g16_msm_create", "g16_msm_destroy", "g16_msm_run_dev",
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
-    "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace",
+    "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace", "g16_h_transform", "g16_h_buffer",
+    "g16_prove_partial_joined",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -104,6 +105,9 @@ def lib():
         L.g16_last_accumulate_ms.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.g16_launch_count.restype = ctypes.c_ulonglong
         L.g16_last_trace.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_h_transform.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        L.g16_h_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_prove_partial_joined.argtypes = [ctypes.c_void_p] * 5
         _lib = L
     return _lib
 
@@ -219,6 +223,21 @@ class ZKey:
         """This shard's five partial MSM sums (768 bytes) -- the unit the multi-GPU gather moves."""
         out = ctypes.create_string_buffer(PARTIAL_BYTES)
         _check(lib().g16_prove_partial(self._h, out))
+        return out.raw
+
+    def h_transform(self, which):
+        """rows a4-a7 for the polynomials in bit mask `which` (1 A, 2 B, 4 C); results stay in the device buffers"""
+        _check(lib().g16_h_transform(self._h, which))
+
+    def h_buffer(self, poly):
+        """-> (device pointer of polynomial buffer 0 A / 1 B / 2 C, this shard's H range lo, n)"""
+        ptr, lo, n = ctypes.c_void_p(), ctypes.c_uint64(), ctypes.c_uint64()
+        _check(lib().g16_h_buffer(self._h, poly, ctypes.byref(ptr), ctypes.byref(lo), ctypes.byref(n)))
+        return ptr.value, lo.value, n.value
+
+    def prove_partial_joined(self, d_a, d_b, d_c):
+        out = ctypes.create_string_buffer(PARTIAL_BYTES)
+        _check(lib().g16_prove_partial_joined(self._h, d_a, d_b, d_c, out))
         return out.raw
 
     def combine(self, partials, r=None, s=None, style=STYLE_RAPIDSNARK):
@@ -455,4 +474,62 @@ def prove_sharded(zk, wtns, r=None, s=None, style=STYLE_RAPIDSNARK, group=None):
     rank 0 and broadcast by the caller)."""
     zk.load_witness(wtns)
     partials = all_gather_partials(zk.prove_partial(), group)
+    return zk.combine(partials, r=r, s=s, style=style)
+
+
+def transform_owner(poly, world):
+    """which rank transforms polynomial 0 A / 1 B / 2 C: spread over the first min(world, 3) ranks"""
+    return poly % min(world, 3)
+
+
+class _DevMem:
+    """a device allocation owned by libg16b200, exposed to torch through __cuda_array_interface__ (no copy)"""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+def exchange_h_slices(zk, group=None):
+    """The second exchange step of a sharded proof: every rank receives, from each polynomial's owner, the slice of
+    that polynomial's coset evaluations covering its own H range (one all-to-all per polynomial; the owner's input is
+    its whole buffer split by the ranks' ranges, everyone else sends nothing).  -> three uint8 device tensors."""
+    import torch
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = zk.domain_size
+    sizes = [(shard_range(n, g, world)[1] - shard_range(n, g, world)[0]) * 32 for g in range(world)]
+    nccl = dist.get_backend(group) == "nccl"
+    xdev = dev if nccl else torch.device("cpu")   # CPU tests (gloo): staged through host memory
+    empty = torch.empty(0, dtype=torch.uint8, device=xdev)
+    out = []
+    for poly in range(3):
+        owner = transform_owner(poly, world)
+        ptr, lo, cnt = zk.h_buffer(poly)
+        assert cnt * 32 == sizes[rank] and lo == shard_range(n, rank, world)[0]
+        recv = torch.empty(sizes[rank], dtype=torch.uint8, device=xdev)
+        if rank == owner:
+            dist.all_to_all_single(recv, torch.as_tensor(_DevMem(ptr, n * 32), device=dev).to(xdev),
+                                   [sizes[rank] if g == owner else 0 for g in range(world)], sizes, group=group)
+        else:
+            dist.all_to_all_single(recv, empty, [sizes[rank] if g == owner else 0 for g in range(world)],
+                                   [0] * world, group=group)
+        out.append(recv.to(dev))
+    return out
+
+
+def prove_sharded_distributed(zk, wtns=None, r=None, s=None, style=STYLE_RAPIDSNARK, group=None):
+    """One proof over all ranks with the three coset transforms spread over the ranks as well: transform the
+    polynomials this rank owns, all-to-all the slices, MSMs on this rank's base ranges + join on its H range, all-gather
+    the 768-byte partials, combine.  NCCL only (the slices are device tensors)."""
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if wtns is not None:
+        zk.load_witness(wtns)
+    mask = sum(1 << p for p in range(3) if transform_owner(p, world) == rank)
+    zk.h_transform(mask)
+    a, b, c = exchange_h_slices(zk, group)
+    import torch
+    torch.cuda.current_stream().synchronize()
+    partials = all_gather_partials(zk.prove_partial_joined(a.data_ptr(), b.data_ptr(), c.data_ptr()), group)
     return zk.combine(partials, r=r, s=s, style=style)

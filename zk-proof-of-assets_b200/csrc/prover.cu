@@ -170,6 +170,7 @@ struct g16_zkey {
     DevBuf pa, pb, pc;         // A, B, C evaluations; pa ends up holding the H scalars
     NttDomain dom;
     cudaStream_t s_main = nullptr, s_msm[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    float t_transform_ms[2] = {0, 0};  // g16_h_transform: r1cs eval, transforms
     cudaStream_t s_pre[4] = {nullptr, nullptr, nullptr, nullptr};  // witness MSMs: digits + sort (high priority)
     cudaEvent_t ev[16];
     bool ev_ok = false;
@@ -497,8 +498,14 @@ static void enqueue_h_pipeline(g16_zkey* zk) {
     G16_CUDA(cudaEventRecord(zk->ev[2], s));
 }
 
+// coset evaluations of this shard's H range, produced elsewhere (transforms spread over ranks): device pointers to
+// H.n elements each; the join (row a8) then runs on the range only
+struct JoinedSlices {
+    const fe_t *a, *b, *c;
+};
+
 // the device part of a proof: five partial MSM sums of this shard, left in the Msm objects' host buffers
-static void prove_device(g16_zkey* zk) {
+static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
     if (!zk->witness_loaded) throw std::runtime_error("no witness loaded");
     G16_CUDA(cudaSetDevice(zk->device));
     auto t0 = std::chrono::steady_clock::now();
@@ -514,7 +521,18 @@ static void prove_device(g16_zkey* zk) {
     zk->B2.msm.stage1(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2]);
     zk->C.msm.stage1(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8,
                      zk->C.mask.as<uint32_t>(), zk->C.n, zk->s_pre[3]);
-    enqueue_h_pipeline(zk);
+    if (js) {
+        G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
+        if (zk->H.n) {
+            ntt_join_kernel<<<(unsigned)((zk->H.n + 255) / 256), 256, 0, zk->s_main>>>(
+                js->a, js->b, js->c, zk->pa.as<fe_t>() + zk->H.lo, (uint32_t)zk->H.n);
+            G16_CUDA(cudaGetLastError());
+            G16_LAUNCHED(1);
+        }
+        G16_CUDA(cudaEventRecord(zk->ev[2], zk->s_main));
+    } else {
+        enqueue_h_pipeline(zk);
+    }
     // H digits + sort stay on the transform stream (highest priority, already ordered after the join); only the
     // accumulation and reductions move to the lowest-priority stream (Msm::stage3)
     G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
@@ -781,6 +799,52 @@ int g16_prove_partial(g16_zkey* zk, uint8_t* partial_out) {
     return guarded([&]() {
         if (!zk || !partial_out) return fail(G16_ERR_GENERIC, "null argument");
         prove_device(zk);
+        export_partial(zk, partial_out);
+        return (int)G16_OK;
+    });
+}
+
+int g16_h_transform(g16_zkey* zk, int which) {
+    return guarded([&]() {
+        if (!zk || (which & ~7)) return fail(G16_ERR_GENERIC, "bad argument");
+        if (!zk->witness_loaded) return fail(G16_ERR_GENERIC, "no witness loaded");
+        G16_CUDA(cudaSetDevice(zk->device));
+        cudaStream_t s = zk->s_main;
+        uint32_t n = zk->domain_size;
+        G16_CUDA(cudaEventRecord(zk->ev[0], s));
+        r1cs_eval_kernel<<<(n + 127) / 128, 128, 0, s>>>(zk->row_ptr.as<uint32_t>(), zk->col.as<uint32_t>(),
+                                                         zk->val.as<fe_t>(), zk->w.as<fe_t>(), n, zk->pa.as<fe_t>(),
+                                                         zk->pb.as<fe_t>(), zk->pc.as<fe_t>());
+        G16_CUDA(cudaGetLastError());
+        G16_LAUNCHED(1);
+        G16_CUDA(cudaEventRecord(zk->ev[1], s));
+        if (which & 1) zk->dom.to_odd_coset(zk->pa.as<fe_t>(), s);
+        if (which & 2) zk->dom.to_odd_coset(zk->pb.as<fe_t>(), s);
+        if (which & 4) zk->dom.to_odd_coset(zk->pc.as<fe_t>(), s);
+        G16_CUDA(cudaEventRecord(zk->ev[2], s));
+        G16_CUDA(cudaStreamSynchronize(s));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, zk->ev[0], zk->ev[1]); zk->t_transform_ms[0] = ms;
+        cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_transform_ms[1] = ms;
+        return (int)G16_OK;
+    });
+}
+
+int g16_h_buffer(g16_zkey* zk, int poly, void** d_ptr, uint64_t* h_lo, uint64_t* h_n) {
+    if (!zk || poly < 0 || poly > 2) return fail(G16_ERR_GENERIC, "bad argument");
+    if (d_ptr) *d_ptr = poly == 0 ? zk->pa.p : poly == 1 ? zk->pb.p : zk->pc.p;
+    if (h_lo) *h_lo = zk->H.lo;
+    if (h_n) *h_n = zk->H.n;
+    return G16_OK;
+}
+
+int g16_prove_partial_joined(g16_zkey* zk, const void* d_a, const void* d_b, const void* d_c, uint8_t* partial_out) {
+    return guarded([&]() {
+        if (!zk || !partial_out || (zk->H.n && (!d_a || !d_b || !d_c))) return fail(G16_ERR_GENERIC, "null argument");
+        JoinedSlices js{(const fe_t*)d_a, (const fe_t*)d_b, (const fe_t*)d_c};
+        prove_device(zk, &js);
+        zk->t_ms[1] = zk->t_transform_ms[0];                // report the transform stage run before the exchange
+        zk->t_ms[2] += zk->t_transform_ms[1];
         export_partial(zk, partial_out);
         return (int)G16_OK;
     });
