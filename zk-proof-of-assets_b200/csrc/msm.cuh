@@ -355,7 +355,7 @@ struct MsmConfig {
     bool sparse = false;  // scalars are witness-like (see msm_pick_c_sparse)
     int c = 0;          // window bits (0 = pick from n)
     uint32_t T = 0;     // max entries per task (0 = from the entry count: about 1024 tasks' worth of work per SM)
-    uint32_t L = 16;    // buckets per reduction chunk
+    uint32_t L = 0;     // buckets per reduction chunk (0 = from the bucket count)
 };
 
 // Counters a finished MSM leaves behind (for bench.py's work model and tests)
@@ -395,7 +395,10 @@ public:
         nb = uint32_t(W) * bpw;
         size_t m_max = n * size_t(W);
         if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
-        L = cfg.L;
+        // level-0 chunks: 16 buckets when there are enough buckets to fill the machine with chunk threads, else 8
+        // (half the dependency chain); level 1 works on bpw/L points only, so its chunks are short (latency, not work)
+        L = cfg.L ? cfg.L : (nb >= (2u << 20) ? 16 : 8);
+        L1 = 4;
         cpw = (bpw + L - 1) / L;
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
@@ -408,7 +411,7 @@ public:
         task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
         cut_list.alloc((m_max / T_MIN + 2) * 4);  // a cut bucket holds more than T >= T_MIN entries
         buckets.alloc(size_t(nb) * sizeof(pt));
-        cpw1 = (cpw + L - 1) / L;
+        cpw1 = (cpw + L1 - 1) / L1;
         chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
         chunk_sum.alloc(size_t(W) * cpw * sizeof(pt));
         chunk2_out.alloc(size_t(W) * cpw1 * sizeof(pt));
@@ -574,7 +577,7 @@ public:
         msm_chunk_reduce_kernel<C, true, false><<<(nchunks + 63) / 64, 64, 0, s>>>(
             buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
         msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
-            chunk_sum.as<pt>(), cpw, L, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
+            chunk_sum.as<pt>(), cpw, L1, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
         const pt* a0 = chunk_out.as<pt>();
         uint32_t n0 = cpw;
         if (cpw >= 32 * SUM_SLICES) {  // long windows: sum the level-0 results in slices first (short dependency chains)
@@ -619,7 +622,7 @@ public:
 
     MsmStats stats;
     int c = 0, W = 0;
-    uint32_t T = 0, L = 0;
+    uint32_t T = 0, L = 0, L1 = 4;
 
 private:
     static constexpr int RED_THREADS = 128;

@@ -170,6 +170,8 @@ struct g16_zkey {
     DevBuf pa, pb, pc;         // A, B, C evaluations; pa ends up holding the H scalars
     NttDomain dom;
     cudaStream_t s_main = nullptr, s_msm[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    HPoint<HFq> fin_a, fin_b1, fin_c;   // finished witness MSMs of the last prove_device
+    HPoint<HFq2> fin_b2;
     float t_transform_ms[2] = {0, 0};  // g16_h_transform: r1cs eval, transforms
     cudaStream_t s_pre[4] = {nullptr, nullptr, nullptr, nullptr};  // witness MSMs: digits + sort (high priority)
     cudaEvent_t ev[16];
@@ -549,10 +551,12 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         G16_CUDA(cudaEventRecord(done, st));
         G16_CUDA(cudaStreamSynchronize(st));
     };
-    auto f0 = std::async(std::launch::async, [&] { drive(&zk->A.msm, zk->s_msm[0], zk->ev[4]); });
-    auto f1 = std::async(std::launch::async, [&] { drive(&zk->B1.msm, zk->s_msm[1], zk->ev[6]); });
-    auto f2 = std::async(std::launch::async, [&] { drive(&zk->B2.msm, zk->s_msm[2], zk->ev[8]); });
-    auto f3 = std::async(std::launch::async, [&] { drive(&zk->C.msm, zk->s_msm[3], zk->ev[10]); });
+    // the witness MSMs finish while the H accumulation still runs: their window Horner chains (255 doublings each, on
+    // the host) are done right here, off the critical path; only the H chain is left for export_partial
+    auto f0 = std::async(std::launch::async, [&] { drive(&zk->A.msm, zk->s_msm[0], zk->ev[4]); zk->fin_a = zk->A.msm.finish<HG1>(); });
+    auto f1 = std::async(std::launch::async, [&] { drive(&zk->B1.msm, zk->s_msm[1], zk->ev[6]); zk->fin_b1 = zk->B1.msm.finish<HG1>(); });
+    auto f2 = std::async(std::launch::async, [&] { drive(&zk->B2.msm, zk->s_msm[2], zk->ev[8]); zk->fin_b2 = zk->B2.msm.finish<HG2>(); });
+    auto f3 = std::async(std::launch::async, [&] { drive(&zk->C.msm, zk->s_msm[3], zk->ev[10]); zk->fin_c = zk->C.msm.finish<HG1>(); });
     std::exception_ptr err;
     try {
         drive(&zk->H.msm, zk->s_msm[4], zk->ev[12]);
@@ -582,18 +586,12 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
 
 static void export_partial(g16_zkey* zk, uint8_t* out) {
     auto t0 = std::chrono::steady_clock::now();
-    // five independent Horner chains (255 doublings each); the G2 one is the longest, so it gets this thread
-    auto fa = std::async(std::launch::async, [zk] { return zk->A.msm.finish<HG1>(); });
-    auto fb = std::async(std::launch::async, [zk] { return zk->B1.msm.finish<HG1>(); });
-    auto fc = std::async(std::launch::async, [zk] { return zk->C.msm.finish<HG1>(); });
-    auto fh = std::async(std::launch::async, [zk] { return zk->H.msm.finish<HG1>(); });
-    HPoint<HFq2> b2 = zk->B2.msm.finish<HG2>();
-    HPoint<HFq> a = fa.get(), b1 = fb.get(), c = fc.get(), h = fh.get();
-    std::memcpy(out, &a, 128);
-    std::memcpy(out + 128, &b1, 128);
-    std::memcpy(out + 256, &c, 128);
+    HPoint<HFq> h = zk->H.msm.finish<HG1>();   // the other four chains were run in prove_device
+    std::memcpy(out, &zk->fin_a, 128);
+    std::memcpy(out + 128, &zk->fin_b1, 128);
+    std::memcpy(out + 256, &zk->fin_c, 128);
     std::memcpy(out + 384, &h, 128);
-    std::memcpy(out + 512, &b2, 256);
+    std::memcpy(out + 512, &zk->fin_b2, 256);
     zk->t_horner_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
 }
 
