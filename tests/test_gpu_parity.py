@@ -142,7 +142,7 @@ def test_msm_g1_scalar_distributions(pkg, kind):
     _msm_case(pkg, False, 3000, 7, scalar_kind=kind, zero_bases=0.3)
 
 
-@pytest.mark.parametrize("c", [4, 7, 11, 13, 16])
+@pytest.mark.parametrize("c", [2, 4, 7, 11, 13, 16, 19])
 def test_msm_g1_window_sizes(pkg, c):
     _msm_case(pkg, False, 2000, 40 + c, msm_c=c)
 

@@ -17,6 +17,7 @@
 //   windows  : the W window sums go to the host, which runs the Horner chain (c doublings per window)
 #pragma once
 #include <cub/cub.cuh>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -163,8 +164,9 @@ static __global__ void msm_make_tasks_kernel(const uint32_t* __restrict__ start,
 // ---------------------------------------------------------------------------------------------------------
 // accumulate: the hot kernel
 // ---------------------------------------------------------------------------------------------------------
-template <class C>
-__global__ void __launch_bounds__(128)
+// MINB = minimum resident CTAs per SM the register allocation must allow (G1: 144 registers give 3; 4 caps them at 128)
+template <class C, int MINB>
+__global__ void __launch_bounds__(128, MINB)
 msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t* __restrict__ vals,
                       const uint32_t* __restrict__ order, const uint32_t* __restrict__ t_begin,
                       const uint32_t* __restrict__ t_len, const uint32_t* __restrict__ t_out, uint32_t nt,
@@ -552,9 +554,19 @@ public:
             size_t tb = task_tmp.bytes;
             G16_CUDA(cub::DeviceRadixSort::SortPairs(task_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
             G16_CUDA(cudaEventRecord(ev_acc0, s));
-            msm_accumulate_kernel<C><<<(nt + 127) / 128, 128, 0, s>>>(
-                bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
-                buckets.as<pt>(), parts.as<pt>());
+            bool launched = false;
+            if constexpr (sizeof(pt) <= 128) {
+                if (acc_minb() == 4) {
+                    msm_accumulate_kernel<C, 4><<<(nt + 127) / 128, 128, 0, s>>>(
+                        bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(),
+                        nt, buckets.as<pt>(), parts.as<pt>());
+                    launched = true;
+                }
+            }
+            if (!launched)
+                msm_accumulate_kernel<C, 1><<<(nt + 127) / 128, 128, 0, s>>>(
+                    bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
+                    buckets.as<pt>(), parts.as<pt>());
             G16_CUDA(cudaEventRecord(ev_acc1, s));
             acc_timed = true;
             G16_CUDA(cudaGetLastError());
@@ -625,6 +637,11 @@ public:
     uint32_t T = 0, L = 0, L1 = 4;
 
 private:
+    static int acc_minb() {   // 4 = the 128-register build of the G1 accumulation (4 CTAs/SM; measured 1-2 % faster than
+                              // the 148-register one); G16_ACC_MINB=1 selects the other for comparison
+        static int v = [] { const char* e = std::getenv("G16_ACC_MINB"); return e ? std::atoi(e) : 4; }();
+        return v;
+    }
     static constexpr int RED_THREADS = 128;
     static constexpr uint32_t SUM_SLICES = 32;
     static void grow(DevBuf& b, size_t bytes) {

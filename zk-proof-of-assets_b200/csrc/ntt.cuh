@@ -50,52 +50,29 @@ ntt_pass_kernel(fe_t* __restrict__ a, int logn, int s_lo, int k, const fe_t* __r
     }
     __syncthreads();
 
-    // Butterfly slots of this thread: BPT per level.  The twiddle of a slot depends on indices only, so the twiddles of
-    // level step+1 are requested before the arithmetic of level step (their L2 latency hides behind the products).
-    constexpr int BPT = NTT_TILE / 2 / NTT_THREADS;
-    auto slot = [&](int step, int i, uint32_t& e0, uint32_t& e1, uint32_t& ex) -> bool {
+    for (int step = 0; step < k; step++) {
         const int r = DIF ? (k - 1 - step) : step;
         const int b = s_lo + r;
-        uint32_t u = threadIdx.x + i * NTT_THREADS;
-        uint32_t qi, tp;
-        if (s_lo > 0) { qi = u & (S - 1); tp = u >> (NTT_TILE_LOG - k); }
-        else { tp = u & ((1u << (k - 1)) - 1); qi = u >> (k - 1); }
-        if (qi >= Sq) return false;
-        uint32_t tl = tp & ((1u << r) - 1), th = tp >> r;
-        uint32_t t0 = (th << (r + 1)) | tl;
-        uint32_t t1 = t0 + (1u << r);
-        uint32_t lo = (q0 + qi) & lomask;
-        uint32_t j = (tl << s_lo) + lo;
-        ex = j << (logn - 1 - b);
-        e0 = s_lo > 0 ? (t0 << (NTT_TILE_LOG - k)) + qi : (qi << k) + t0;
-        e1 = s_lo > 0 ? (t1 << (NTT_TILE_LOG - k)) + qi : (qi << k) + t1;
-        return true;
-    };
-    auto twiddle = [&](uint32_t ex) -> fe_t {   // ex != 0
-        return INV ? ldg_fe(tw + ((n >> 1) - ex)) : ldg_fe(tw + ex);   // INV: -w^(n/2-ex) = w^-ex, negated at use
-    };
-    fe_t wcur[BPT], wnext[BPT];
-#pragma unroll
-    for (int i = 0; i < BPT; i++) {
-        uint32_t e0, e1, ex;
-        if (k > 0 && slot(0, i, e0, e1, ex) && ex) wcur[i] = twiddle(ex);
-    }
-    for (int step = 0; step < k; step++) {
-        if (step + 1 < k) {
-#pragma unroll
-            for (int i = 0; i < BPT; i++) {
-                uint32_t e0, e1, ex;
-                if (slot(step + 1, i, e0, e1, ex) && ex) wnext[i] = twiddle(ex);
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < BPT; i++) {
-            uint32_t e0, e1, ex;
-            if (!slot(step, i, e0, e1, ex)) continue;
+        for (uint32_t u = threadIdx.x; u < NTT_TILE / 2; u += NTT_THREADS) {
+            uint32_t qi, tp;
+            if (s_lo > 0) { qi = u & (S - 1); tp = u >> (NTT_TILE_LOG - k); }
+            else { tp = u & ((1u << (k - 1)) - 1); qi = u >> (k - 1); }
+            if (qi >= Sq) continue;
+            uint32_t tl = tp & ((1u << r) - 1), th = tp >> r;
+            uint32_t t0 = (th << (r + 1)) | tl;
+            uint32_t t1 = t0 + (1u << r);
+            uint32_t lo = (q0 + qi) & lomask;
+            uint32_t j = (tl << s_lo) + lo;
+            uint32_t ex = j << (logn - 1 - b);
+            uint32_t e0 = s_lo > 0 ? (t0 << (NTT_TILE_LOG - k)) + qi : (qi << k) + t0;
+            uint32_t e1 = s_lo > 0 ? (t1 << (NTT_TILE_LOG - k)) + qi : (qi << k) + t1;
             fe_t x = sh[e0], y = sh[e1];
+            fe_t w;
             bool unit = (ex == 0);
-            fe_t w = wcur[i];
-            if (INV && !unit) w = Fr::neg(w);
+            if (!unit) {
+                if (INV) w = Fr::neg(ldg_fe(tw + ((n >> 1) - ex)));
+                else w = ldg_fe(tw + ex);
+            }
             if (DIF) {
                 fe_t d = Fr::sub(x, y);
                 sh[e0] = Fr::add(x, y);
@@ -107,8 +84,6 @@ ntt_pass_kernel(fe_t* __restrict__ a, int logn, int s_lo, int k, const fe_t* __r
             }
         }
         __syncthreads();
-#pragma unroll
-        for (int i = 0; i < BPT; i++) wcur[i] = wnext[i];
     }
 
     for (uint32_t e = threadIdx.x; e < NTT_TILE; e += NTT_THREADS) {

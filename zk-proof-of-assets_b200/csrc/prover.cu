@@ -544,22 +544,27 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
     // per MSM drives those, so a wait on one stream never delays the launches of another (the H chain in particular
     // must be enqueued the moment the transforms finish).
     int dev = zk->device;
-    auto drive = [dev](auto* msm, cudaStream_t st, cudaEvent_t done) {
+    // G16_ACC_AFTER_NTT=1 (experiment): the witness accumulations wait for the transforms, so that the transforms run
+    // with only HBM-bound sorts beside them and the accumulations fill the integer pipe while the H entries are sorted
+    static const bool acc_after_ntt = [] { const char* e = std::getenv("G16_ACC_AFTER_NTT"); return e && std::atoi(e) != 0; }();
+    cudaEvent_t ntt_done = zk->ev[2];
+    auto drive = [dev, ntt_done](auto* msm, cudaStream_t st, cudaEvent_t done, bool gate) {
         G16_CUDA(cudaSetDevice(dev));
         msm->stage2();
+        if (gate) G16_CUDA(cudaStreamWaitEvent(st, ntt_done, 0));
         msm->stage3(st);
         G16_CUDA(cudaEventRecord(done, st));
         G16_CUDA(cudaStreamSynchronize(st));
     };
     // the witness MSMs finish while the H accumulation still runs: their window Horner chains (255 doublings each, on
     // the host) are done right here, off the critical path; only the H chain is left for export_partial
-    auto f0 = std::async(std::launch::async, [&] { drive(&zk->A.msm, zk->s_msm[0], zk->ev[4]); zk->fin_a = zk->A.msm.finish<HG1>(); });
-    auto f1 = std::async(std::launch::async, [&] { drive(&zk->B1.msm, zk->s_msm[1], zk->ev[6]); zk->fin_b1 = zk->B1.msm.finish<HG1>(); });
-    auto f2 = std::async(std::launch::async, [&] { drive(&zk->B2.msm, zk->s_msm[2], zk->ev[8]); zk->fin_b2 = zk->B2.msm.finish<HG2>(); });
-    auto f3 = std::async(std::launch::async, [&] { drive(&zk->C.msm, zk->s_msm[3], zk->ev[10]); zk->fin_c = zk->C.msm.finish<HG1>(); });
+    auto f0 = std::async(std::launch::async, [&] { drive(&zk->A.msm, zk->s_msm[0], zk->ev[4], acc_after_ntt); zk->fin_a = zk->A.msm.finish<HG1>(); });
+    auto f1 = std::async(std::launch::async, [&] { drive(&zk->B1.msm, zk->s_msm[1], zk->ev[6], acc_after_ntt); zk->fin_b1 = zk->B1.msm.finish<HG1>(); });
+    auto f2 = std::async(std::launch::async, [&] { drive(&zk->B2.msm, zk->s_msm[2], zk->ev[8], acc_after_ntt); zk->fin_b2 = zk->B2.msm.finish<HG2>(); });
+    auto f3 = std::async(std::launch::async, [&] { drive(&zk->C.msm, zk->s_msm[3], zk->ev[10], acc_after_ntt); zk->fin_c = zk->C.msm.finish<HG1>(); });
     std::exception_ptr err;
     try {
-        drive(&zk->H.msm, zk->s_msm[4], zk->ev[12]);
+        drive(&zk->H.msm, zk->s_msm[4], zk->ev[12], false);
     } catch (...) {
         err = std::current_exception();
     }
