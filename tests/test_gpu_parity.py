@@ -167,6 +167,62 @@ def test_msm_against_oracle_pippenger_inputs(pkg):
     assert pkg.msm_host(False, b"", b"", 0) == bytes(64)  # empty input -> infinity
 
 
+def test_msm_repeated_and_opposite_bases(pkg):
+    """the same base many times in one bucket, and P next to -P: the doubling / cancellation cases of the group law
+    (XYZZ mixed addition, and the batched-affine pair round when G16_PAIR_MERGE is on)"""
+    rng = random.Random(99)
+    ks = [5, 5, R - 5, 5, 7, 7, 7, 7, R - 7, 11, R - 11, 11, 13] * 40
+    rng.shuffle(ks)
+    for ss in ([1] * len(ks), [3] * len(ks), [rng.choice([1, 2, R - 1]) for _ in ks]):
+        for is_g2 in (False, True):
+            bases = pkg.fixed_base(is_g2, b"".join(map(le, ks)), len(ks))
+            got = pkg.msm_host(is_g2, bases, b"".join(map(le, ss)), len(ks), msm_c=4)
+            e = sum(k * s for k, s in zip(ks, ss)) % R
+            if is_g2:
+                assert binfile.dec_g2(got) == bn.G2.mul(bn.G2_GEN, e)
+            else:
+                assert binfile.dec_g1(got) == bn.G1.mul(bn.G1_GEN, e)
+
+
+MERGE_WORKER = r'''
+import os, sys, random
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
+from conftest import load_pkg
+from oracle import bn254 as bn, binfile
+pkg = load_pkg()
+R = bn.R
+le = lambda x: int(x).to_bytes(32, "little")
+rng = random.Random(5)
+cases = [([5, 5, R - 5, 5, 7, 7, 7, 7, R - 7, 11, R - 11, 11, 13] * 40, None, 4),
+         ([rng.randrange(1, R) for _ in range(6000)], "uniform", 0),
+         ([rng.randrange(1, R) for _ in range(6001)], "witness", 9)]
+for ks, kind, c in cases:
+    if kind is None:
+        ss = [rng.choice([1, 2, R - 1]) for _ in ks]
+    elif kind == "uniform":
+        ss = [rng.randrange(R) for _ in ks]
+    else:
+        ss = [rng.choice([0, 1, 1, rng.randrange(1 << 64), rng.randrange(R), R - 1]) for _ in ks]
+    e = sum(k * s for k, s in zip(ks, ss)) % R
+    for is_g2 in (False, True):
+        bases = pkg.fixed_base(is_g2, b"".join(map(le, ks)), len(ks))
+        got = pkg.msm_host(is_g2, bases, b"".join(map(le, ss)), len(ks), msm_c=c)
+        want = bn.G2.mul(bn.G2_GEN, e) if is_g2 else bn.G1.mul(bn.G1_GEN, e)
+        assert (binfile.dec_g2(got) if is_g2 else binfile.dec_g1(got)) == want, (kind, is_g2)
+print("merge ok")
+'''
+
+
+def test_msm_with_pair_merge_round(tmp_path):
+    """the optional batched-affine pair round (G16_PAIR_MERGE=1, read once per process, hence the subprocess):
+    generic pairs, doublings, opposite points, odd bucket starts, G1 and G2 -- same sums as the closed form"""
+    import sys
+    (tmp_path / "w.py").write_text(MERGE_WORKER)
+    env = dict(os.environ, G16_PAIR_MERGE="1", G16_PAIR_MERGE_MIN="0")
+    p = subprocess.run([sys.executable, str(tmp_path / "w.py"), ROOT], env=env, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0 and "merge ok" in p.stdout, p.stdout + p.stderr
+
+
 def test_msm_linearity_at_scale(pkg):
     """size-independent property at 2^20: MSM(P, s) + MSM(P, t) == MSM(P, s + t)"""
     import numpy as np

@@ -26,6 +26,10 @@
 
 namespace g16 {
 
+// entry values: bit 31 = negate the base, bit 30 = the index points into the merged-pair array (msm_pair_merge_kernel)
+constexpr uint32_t MSM_MERGED_FLAG = 0x40000000u;
+constexpr uint32_t MSM_INDEX_MASK = 0x3fffffffu;
+
 static inline int msm_num_windows(int c) { return (255 + c - 1) / c; }
 
 // heuristic window width: bucket reduction (2 full adds per bucket per window) stays a few % of accumulation
@@ -167,10 +171,11 @@ static __global__ void msm_make_tasks_kernel(const uint32_t* __restrict__ start,
 // MINB = minimum resident CTAs per SM the register allocation must allow (G1: 144 registers give 3; 4 caps them at 128)
 template <class C, int MINB>
 __global__ void __launch_bounds__(128, MINB)
-msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t* __restrict__ vals,
-                      const uint32_t* __restrict__ order, const uint32_t* __restrict__ t_begin,
-                      const uint32_t* __restrict__ t_len, const uint32_t* __restrict__ t_out, uint32_t nt,
-                      typename C::pt* __restrict__ buckets, typename C::pt* __restrict__ parts) {
+msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const typename C::aff* __restrict__ merged,
+                      const uint32_t* __restrict__ vals, const uint32_t* __restrict__ order,
+                      const uint32_t* __restrict__ t_begin, const uint32_t* __restrict__ t_len,
+                      const uint32_t* __restrict__ t_out, uint32_t nt, typename C::pt* __restrict__ buckets,
+                      typename C::pt* __restrict__ parts) {
     typedef typename C::aff aff;
     typedef typename C::pt pt;
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -178,22 +183,170 @@ msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t*
     uint32_t j = order[tid];
     uint32_t e = t_begin[j], len = t_len[j], out = t_out[j];
     pt acc = C::identity();
+    // an entry is a base index (bit 31 = negate) or, after the pair merge, MSM_MERGED_FLAG | index of a merged point
+    auto fetch = [&](uint32_t v) -> aff {
+        return (v & MSM_MERGED_FLAG) ? merged[v & MSM_INDEX_MASK] : bases[v & MSM_INDEX_MASK];
+    };
     uint32_t v = vals[e];
-    aff q = bases[v & 0x7fffffffu];
+    aff q = fetch(v);
     for (uint32_t k = 0; k < len; k++) {
         uint32_t vn = 0;
         aff qn = q;
         if (k + 1 < len) {  // prefetch the next point while this one is added
             vn = vals[e + k + 1];
-            qn = bases[vn & 0x7fffffffu];
+            qn = fetch(vn);
         }
         if (v >> 31) q.y = C::field::neg(q.y);
-        C::madd(acc, q);
+        if (!((v & MSM_MERGED_FLAG) && C::is_inf(q))) C::madd(acc, q);   // a merged pair of opposite points is infinity
         v = vn;
         q = qn;
     }
     if (out >> 31) parts[out & 0x7fffffffu] = acc;
     else buckets[out] = acc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// pair merge: one round of batched-affine addition in front of the accumulation
+// ---------------------------------------------------------------------------------------------------------
+// Sorted entries that share a bucket and sit on absolute positions (2g, 2g+1) are added in AFFINE coordinates:
+// (x3, y3) = (L^2 - x1 - x2, L (x1 - x3) - y1), L = (y2 - y1) / (x2 - x1), with the inversions batched by Montgomery's
+// trick over the P <= 256 pair slots of a thread (one Fermat inversion per thread).  That is 1 (prefix product) + 384/P
+// (inversion) + 2 (unwinding) + 3 (L, L^2, y3) = about 7.5 field products per addition against 10 for the XYZZ mixed
+// addition, on half of all additions.  The merged points go to `merged`, the entry list is rewritten compacted per
+// bucket (an entry is a base index | sign, or MERGED_FLAG | merged index), and the accumulation runs on the shorter
+// lists.  A bucket that starts on an odd position keeps its first entry single; so does one that ends on an even one.
+// output position of input position p of a bucket that starts at s
+static __device__ __forceinline__ uint32_t msm_merged_pos(uint32_t s, uint32_t p) { return s + ((p - s + (s & 1u)) >> 1); }
+
+static __global__ void msm_merged_end_kernel(const uint32_t* __restrict__ start, uint32_t* __restrict__ end, uint32_t nb) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nb) return;
+    uint32_t s = start[k], e = end[k];
+    if (e > s) end[k] = msm_merged_pos(s, e - 1) + 1;
+}
+
+// kind of a pair: 0 = generic (d = x2 - x1), 1 = doubling (d = 2 y1), 2 = opposite points (sum = infinity, d = 1)
+template <class C>
+static __device__ __forceinline__ int msm_pair_den(const typename C::aff& a, const typename C::aff& b, typename C::fe& d) {
+    typedef typename C::field F;
+    d = F::sub(b.x, a.x);
+    if (!F::is_zero(d)) return 0;
+    if (F::eq(a.y, b.y)) {
+        d = F::dbl(a.y);
+        return 1;
+    }
+    d = F::one();
+    return 2;
+}
+
+// one pair slot as loaded from memory (the loads of slot j+1 are issued before the arithmetic of slot j)
+template <class C>
+struct MsmPairSlot {
+    typename C::aff a, b;
+    uint32_t k0, v0, v1;
+    bool live, pair;   // live: g < nslots; pair: both positions exist and share a bucket
+};
+
+template <class C>
+static __device__ __forceinline__ MsmPairSlot<C> msm_pair_fetch(const typename C::aff* __restrict__ bases,
+                                                                const uint32_t* __restrict__ keys,
+                                                                const uint32_t* __restrict__ vals, uint32_t m,
+                                                                uint32_t nslots, uint32_t g) {
+    MsmPairSlot<C> s;
+    s.live = g < nslots;
+    s.pair = false;
+    if (!s.live) return s;
+    uint32_t p0 = 2 * g, p1 = p0 + 1;
+    s.k0 = keys[p0];
+    s.v0 = vals[p0];
+    s.v1 = 0;
+    if (p1 < m) {
+        s.v1 = vals[p1];
+        s.pair = keys[p1] == s.k0;
+    }
+    if (s.pair) {
+        s.a = bases[s.v0 & MSM_INDEX_MASK];
+        s.b = bases[s.v1 & MSM_INDEX_MASK];
+        if (s.v0 >> 31) s.a.y = C::field::neg(s.a.y);
+        if (s.v1 >> 31) s.b.y = C::field::neg(s.b.y);
+    }
+    return s;
+}
+
+// Thread t owns the slots t, t + T, t + 2T, ... (coalesced across a warp); the batch of one inversion is a thread's
+// per_thread slots.  It has to be large: the Fermat chain is 384 sequential products PER LANE, so it is amortised
+// only over the slots of that lane (a warp-wide batch with one shared inversion was measured 3x slower: the
+// inversion's instruction stream costs a warp the same whether one lane or thirty-two use its result).
+template <class C>
+__global__ void __launch_bounds__(128)
+msm_pair_merge_kernel(const typename C::aff* __restrict__ bases, const uint32_t* __restrict__ keys,
+                      const uint32_t* __restrict__ vals, const uint32_t* __restrict__ start, uint32_t m, uint32_t nslots,
+                      uint32_t per_thread, typename C::fe* __restrict__ prefix, typename C::aff* __restrict__ merged,
+                      uint32_t* __restrict__ vals_out) {
+    typedef typename C::field F;
+    typedef typename C::fe fe;
+    typedef typename C::aff aff;
+    typedef MsmPairSlot<C> slot_t;
+    const uint32_t T = gridDim.x * blockDim.x;
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    // forward: prefix products of the denominators of this thread's slots
+    fe prod = F::one();
+    {
+        slot_t cur = msm_pair_fetch<C>(bases, keys, vals, m, nslots, t);
+        for (uint32_t j = 0; j < per_thread; j++) {
+            uint32_t g = t + j * T;
+            slot_t nxt = msm_pair_fetch<C>(bases, keys, vals, m, nslots, j + 1 < per_thread ? g + T : nslots);
+            if (cur.pair) {
+                fe d;
+                msm_pair_den<C>(cur.a, cur.b, d);
+                prefix[g] = prod;
+                prod = F::mul(prod, d);
+            }
+            cur = nxt;
+        }
+    }
+    fe inv = F::inv(prod);
+    // backward: unwind the inverses, finish the additions, rewrite the entries
+    uint32_t jl = per_thread - 1;
+    slot_t cur = msm_pair_fetch<C>(bases, keys, vals, m, nslots, t + jl * T);
+    fe pre = cur.pair ? prefix[t + jl * T] : F::one();
+    for (uint32_t j = per_thread; j-- > 0;) {
+        uint32_t g = t + j * T;
+        slot_t nxt = msm_pair_fetch<C>(bases, keys, vals, m, nslots, j > 0 ? g - T : nslots);
+        fe npre = nxt.pair ? prefix[g - T] : F::one();
+        if (cur.live) {
+            uint32_t p0 = 2 * g, p1 = p0 + 1;
+            if (!cur.pair) {
+                // two singles: the last entry of one bucket, the first of the next (or the odd entry that ends the list)
+                vals_out[msm_merged_pos(start[cur.k0], p0)] = cur.v0;
+                if (p1 < m) vals_out[p1] = cur.v1;   // start of its bucket: position unchanged
+            } else {
+                fe d;
+                int kind = msm_pair_den<C>(cur.a, cur.b, d);
+                fe dinv = F::mul(inv, pre);
+                inv = F::mul(inv, d);
+                aff r;
+                if (kind == 2) {
+                    r.x = F::zero();
+                    r.y = F::zero();   // infinity: the accumulation skips it
+                } else {
+                    fe num;
+                    if (kind == 0) num = F::sub(cur.b.y, cur.a.y);
+                    else {
+                        fe xx = F::sqr(cur.a.x);
+                        num = F::add(F::dbl(xx), xx);
+                    }
+                    fe lam = F::mul(num, dinv);
+                    r.x = F::sub(F::sub(F::sqr(lam), cur.a.x), cur.b.x);
+                    r.y = F::sub(F::mul(lam, F::sub(cur.a.x, r.x)), cur.a.y);
+                }
+                merged[g] = r;
+                vals_out[msm_merged_pos(start[cur.k0], p0)] = MSM_MERGED_FLAG | g;
+            }
+        }
+        cur = nxt;
+        pre = npre;
+    }
 }
 
 // block-wide tree sum of XYZZ points held one per thread; result in every thread.
@@ -372,6 +525,7 @@ class Msm {
 public:
     typedef typename C::aff aff;
     typedef typename C::pt pt;
+    typedef typename C::fe fe;
     static constexpr uint32_t T_MIN = sizeof(pt) > 128 ? 16 : 32;
     static constexpr uint32_t T_MAX = 512;
 
@@ -381,6 +535,8 @@ public:
         if (h_windows) cudaFreeHost(h_windows);
         if (ev_acc0) cudaEventDestroy(ev_acc0);
         if (ev_acc1) cudaEventDestroy(ev_acc1);
+        if (ev_mrg0) cudaEventDestroy(ev_mrg0);
+        if (ev_mrg1) cudaEventDestroy(ev_mrg1);
         for (auto& e : ev_t)
             if (e) cudaEventDestroy(e);
     }
@@ -431,6 +587,8 @@ public:
         if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
         if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
         if (!ev_acc1) G16_CUDA(cudaEventCreate(&ev_acc1));
+        if (!ev_mrg0) G16_CUDA(cudaEventCreate(&ev_mrg0));
+        if (!ev_mrg1) G16_CUDA(cudaEventCreate(&ev_mrg1));
         for (auto& e : ev_t)
             if (!e) G16_CUDA(cudaEventCreate(&e));
     }
@@ -449,8 +607,9 @@ public:
 
     // duration of the last accumulate kernel (CUDA events on its own stream); valid once the stream is synchronised
     float accumulate_ms() const {
-        float ms = 0;
+        float ms = 0, mg = 0;
         if (!acc_timed || cudaEventElapsedTime(&ms, ev_acc0, ev_acc1) != cudaSuccess) return 0;
+        if (merged_slots && cudaEventElapsedTime(&mg, ev_mrg0, ev_mrg1) == cudaSuccess) ms += mg;  // the pair merge is part of it
         return ms;
     }
 
@@ -483,7 +642,7 @@ public:
         if (T == 0) {
             // enough tasks to fill the machine several times over: a task is one thread's dependency chain, so its
             // length bounds the kernel's tail; a cut bucket costs one extra full addition per task
-            size_t t = m / slots;
+            size_t t = (merge_enabled() ? m / 2 : m) / slots;
             T = uint32_t(t < T_MIN ? T_MIN : t > T_MAX ? T_MAX : t);
         }
         if (T < T_MIN) T = T_MIN;
@@ -504,6 +663,27 @@ public:
         G16_CUDA(cudaMemsetAsync(end.p, 0, size_t(nb) * 4, s));
         msm_bounds_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s>>>(sorted_keys, (uint32_t)m, start.as<uint32_t>(),
                                                                       end.as<uint32_t>());
+        merged_slots = 0;
+        if (merge_enabled() && m >= merge_min() && ((m + 1) / 2) * (sizeof(aff) + sizeof(fe)) <= (size_t(24) << 30)) {
+            // one round of batched-affine pair additions in front of the accumulation (see msm_pair_merge_kernel)
+            uint32_t nslots = uint32_t((m + 1) / 2);
+            grow(merged, size_t(nslots) * sizeof(aff));
+            grow(prefix, size_t(nslots) * sizeof(fe));
+            uint32_t want = uint32_t(slots / 2);                 // threads that fill the machine
+            uint32_t per = (nslots + want - 1) / want;
+            per = per < 32 ? 32 : per > 256 ? 256 : per;         // slots per thread = the inversion's batch
+            uint32_t blocks = ((nslots + per - 1) / per + 127) / 128;
+            per = (nslots + blocks * 128 - 1) / (blocks * 128);
+            G16_CUDA(cudaEventRecord(ev_mrg0, s));
+            msm_pair_merge_kernel<C><<<blocks, 128, 0, s>>>(bases, sorted_keys, sorted_vals, start.as<uint32_t>(), (uint32_t)m,
+                                                            nslots, per, prefix.as<fe>(), merged.as<aff>(), dv.Alternate());
+            G16_CUDA(cudaEventRecord(ev_mrg1, s));
+            msm_merged_end_kernel<<<(nb + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb);
+            G16_CUDA(cudaGetLastError());
+            G16_LAUNCHED(2);
+            sorted_vals = dv.Alternate();
+            merged_slots = nslots;
+        }
         uint32_t* cut_count = counters.as<uint32_t>() + 4;  // byte offset 16
         msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb, T,
                                                                     ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
@@ -558,14 +738,14 @@ public:
             if constexpr (sizeof(pt) <= 128) {
                 if (acc_minb() == 4) {
                     msm_accumulate_kernel<C, 4><<<(nt + 127) / 128, 128, 0, s>>>(
-                        bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(),
+                        bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(),
                         nt, buckets.as<pt>(), parts.as<pt>());
                     launched = true;
                 }
             }
             if (!launched)
                 msm_accumulate_kernel<C, 1><<<(nt + 127) / 128, 128, 0, s>>>(
-                    bases, sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
+                    bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
                     buckets.as<pt>(), parts.as<pt>());
             G16_CUDA(cudaEventRecord(ev_acc1, s));
             acc_timed = true;
@@ -642,6 +822,14 @@ private:
         static int v = [] { const char* e = std::getenv("G16_ACC_MINB"); return e ? std::atoi(e) : 4; }();
         return v;
     }
+    static bool merge_enabled() {   // G16_PAIR_MERGE=1: batched-affine pair round in front of the accumulation
+        static bool v = [] { const char* e = std::getenv("G16_PAIR_MERGE"); return e && std::atoi(e) != 0; }();
+        return v;
+    }
+    static size_t merge_min() {     // fewest entries for which the pair round pays (G16_PAIR_MERGE_MIN overrides; tests use 0)
+        static size_t v = [] { const char* e = std::getenv("G16_PAIR_MERGE_MIN"); return e ? size_t(std::atoll(e)) : size_t(1) << 20; }();
+        return v;
+    }
     static constexpr int RED_THREADS = 128;
     static constexpr uint32_t SUM_SLICES = 32;
     static void grow(DevBuf& b, size_t bytes) {
@@ -659,11 +847,13 @@ private:
     cudaStream_t stream = 0;
     uint32_t *sorted_keys = nullptr, *sorted_vals = nullptr;
     DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
-        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, chunk_out, chunk_sum, chunk2_out, slice_out,
+        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, merged, prefix, chunk_out, chunk_sum, chunk2_out, slice_out,
         window_out, counters, cub_tmp,
         task_tmp;
     unsigned long long* h_counters = nullptr;
     pt* h_windows = nullptr;
+    cudaEvent_t ev_mrg0 = nullptr, ev_mrg1 = nullptr;
+    uint32_t merged_slots = 0;
     cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr, ev_t[4] = {nullptr, nullptr, nullptr, nullptr};
     bool acc_timed = false;
 };
