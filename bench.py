@@ -292,6 +292,8 @@ def run_b200(args):
         peaks = measured_peaks()
         traffic = measured_traffic(args.workload)
         acc_alg_bytes = 68 * g1_adds + 132 * g2_adds      # one base record + one 4-byte entry per mixed addition
+        h_ms = acc_ms["H"] / steps
+        h_ops = MODMUL_OPS * G1_MADD_MODMULS * stats["H"]["additions"]
         imad_peak = pkg.bench_int_pipe(1)            # wide multiply-adds per second, measured on this GPU now
         modmul_peak = pkg.bench_int_pipe(2)          # dependent-chain Montgomery products per second
         hbm_peak = peaks.get("hbm_gbs")
@@ -319,16 +321,26 @@ def run_b200(args):
             "e2e": {"value": ncons * steps * jobs / e2e_s, "unit": "constraints/s", "ms_per_step": e2e_s / steps * 1e3,
                     "h2d_bytes_per_step": len(wtns), "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "msm_accumulate_kernel (bucket accumulation, all five MSMs of a step)",
-                         "bound": "int", "achieved": int_ops / (acc_total_ms * 1e-3) / 1e12 if acc_total_ms else None,
+            # the dominant kernel = the bucket accumulation of the H MSM (one launch per step, the largest MSM at every
+            # config); CUDA events on its own stream around that launch.  The four witness-MSM launches overlap the
+            # transforms and each other, so their event times are not kernel durations: they are listed apart.
+            "roofline": {"kernel": "msm_accumulate_kernel<G1>, H MSM launch (bucket accumulation; dominant kernel)",
+                         "bound": "int", "achieved": h_ops / (h_ms * 1e-3) / 1e12 if h_ms else None,
                          "peak": imad_peak / 1e12, "unit": "T wide-IMAD/s",
-                         "frac": (int_ops / (acc_total_ms * 1e-3)) / imad_peak if acc_total_ms else None,
+                         "frac": (h_ops / (h_ms * 1e-3)) / imad_peak if h_ms else None,
+                         "units_per_launch": stats["H"]["additions"], "ops_per_unit": MODMUL_OPS * G1_MADD_MODMULS,
+                         "ms_per_launch": h_ms,
                          "peak_source": "g16_bench_int_pipe(1): IMAD.WIDE.U32 carry chains, measured in this run "
                                         "(MEASURED_PEAKS.json has no integer figure)",
-                         "modmul_peak_per_s": modmul_peak, "share_of_step": acc_total_ms / (resident_s / steps * 1e3),
-                         "algorithmic_bytes": acc_alg_bytes,
-                         "traffic": traffic.get("msm_accumulate", {}).get("bytes_per_step"),
-                         "traffic_source": traffic.get("msm_accumulate", {}).get("source")},
+                         "modmul_peak_per_s": modmul_peak, "share_of_step": h_ms / (resident_s / steps * 1e3),
+                         "algorithmic_bytes": 68 * stats["H"]["additions"],
+                         "traffic": traffic.get("msm_accumulate_H", {}).get("bytes_per_launch"),
+                         "traffic_source": traffic.get("msm_accumulate_H", {}).get("source")},
+            "roofline_all_accumulate": {"kernel": "all five msm_accumulate launches of a step (overlapped with other streams)",
+                                        "achieved": int_ops / (acc_total_ms * 1e-3) / 1e12 if acc_total_ms else None,
+                                        "frac": (int_ops / (acc_total_ms * 1e-3)) / imad_peak if acc_total_ms else None,
+                                        "sum_of_event_ms": acc_total_ms, "algorithmic_bytes": acc_alg_bytes,
+                                        "traffic": traffic.get("msm_accumulate", {}).get("bytes_per_step")},
             "roofline_ntt": {"kernel": "ntt_pass_kernel x passes + r1cs/join (H pipeline)", "bound": "hbm",
                              "achieved": ntt_gbs, "peak": hbm_peak, "unit": "GB/s",
                              "frac": ntt_gbs / hbm_peak if hbm_peak else None,

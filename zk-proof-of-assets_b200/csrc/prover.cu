@@ -11,6 +11,7 @@
 #include <chrono>
 #include <future>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -900,17 +901,36 @@ int g16_prove_files(const char* zkey_path, const char* wtns_path, const char* pr
         if (opts) o = *opts;
         else g16_opts_default(&o);
         o.shard_count = 1;
+        // G16_VERBOSE: where the wall time of one command-line call goes (the reference's figure is GNU time around the
+        // whole process, scripts/lib/cmd_executor.sh:6,17)
+        const bool verbose = std::getenv("G16_VERBOSE") != nullptr;
+        auto t0 = std::chrono::steady_clock::now();
+        auto lap = [&](const char* what) {
+            if (!verbose) return;
+            auto t1 = std::chrono::steady_clock::now();
+            std::fprintf(stderr, "prover: %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+            t0 = t1;
+        };
         MappedFile fz(zkey_path), fw(wtns_path);
+        lap("map files");
+        set_device(o.device);
+        G16_CUDA(cudaFree(nullptr));
+        lap("CUDA context");
         std::unique_ptr<g16_zkey> zk(zkey_build(fz.p, fz.len, &o));
+        lap("key: parse + upload + tables");
         witness_load(zk.get(), fw.p, fw.len);
+        lap("witness: parse + upload");
         uint8_t partial[G16_PARTIAL_BYTES];
         auto blind = std::async(std::launch::async, [&] { return make_blind(zk.get(), o); });
         prove_device(zk.get());
         export_partial(zk.get(), partial);
         std::string proof, pub;
         combine(zk.get(), partial, 1, o, blind.get(), proof, pub);
+        lap("prove (first call, cold)");
         write_file(proof_path, proof);
         write_file(public_path, pub);
+        zk.reset();
+        lap("write outputs + release");
         return (int)G16_OK;
     });
 }
