@@ -7,10 +7,13 @@ python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_fin
 python bench.py --workload l1-16sigs --steps 3 --no-cpu-baseline > gpurun_out/bench_l1_16_final.json 2> gpurun_out/bench_l1_16_final.err
 B="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-verify"
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_final.csv $B > gpurun_out/ncu_final.log 2>&1
-mkdir -p /tmp/prof
-ncu --set full --clock-control none --import-source on -k regex:msm_accumulate -s 15 -c 5 -o /tmp/prof/acc $B > gpurun_out/ncu_acc.log 2>&1
-ncu -i /tmp/prof/acc.ncu-rep --page raw --csv > gpurun_out/acc_raw_final.csv
-ncu --set full --clock-control none --import-source on -k regex:ntt_pass -s 54 -c 6 -o /tmp/prof/ntt $B > gpurun_out/ncu_ntt.log 2>&1
-ncu -i /tmp/prof/ntt.ncu-rep --page raw --csv > gpurun_out/ntt_raw_final.csv
+
+
+
+
+
 python bench_cli.py > gpurun_out/cli_wall_final.json 2> gpurun_out/cli_wall_final.err
 ls -la gpurun_out | tail -15
+C=/tmp/g16_bench_cache; P=zk-proof-of-assets_b200/prover
+for i in 1 2; do G16_VERBOSE=1 $P $C/c2-layer-one.zkey $C/c2-layer-one.wtns /tmp/p.json /tmp/u.json; done 2> gpurun_out/cli_verbose.log
+cat gpurun_out/cli_verbose.log

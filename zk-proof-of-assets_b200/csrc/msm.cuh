@@ -42,6 +42,26 @@ static inline int msm_pick_c(size_t n) {
     return c;
 }
 
+// block-wide tree sum of XYZZ points held one per thread; result in every thread.
+// The staging array is STATIC shared memory (16 KB G1 / 32 KB G2 at 128 threads): with an `extern __shared__`
+// byte array cast to pt*, nvcc 12.9 drops the first 16-byte store of `sh[threadIdx.x] = acc` (seen in the PTX).
+template <class C, int THREADS>
+__device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
+    __shared__ typename C::pt sh[THREADS];
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = THREADS / 2; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) {
+            typename C::pt a = sh[threadIdx.x];
+            C::add(a, sh[threadIdx.x + s]);
+            sh[threadIdx.x] = a;
+        }
+        __syncthreads();
+    }
+    acc = sh[0];
+}
+
+#ifdef G16_MSM_INSTANTIATE   // the kernels are compiled in msm.cu only (one copy in the library, one module to load)
 // ---------------------------------------------------------------------------------------------------------
 // digits
 // ---------------------------------------------------------------------------------------------------------
@@ -349,25 +369,6 @@ msm_pair_merge_kernel(const typename C::aff* __restrict__ bases, const uint32_t*
     }
 }
 
-// block-wide tree sum of XYZZ points held one per thread; result in every thread.
-// The staging array is STATIC shared memory (16 KB G1 / 32 KB G2 at 128 threads): with an `extern __shared__`
-// byte array cast to pt*, nvcc 12.9 drops the first 16-byte store of `sh[threadIdx.x] = acc` (seen in the PTX).
-template <class C, int THREADS>
-__device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
-    __shared__ typename C::pt sh[THREADS];
-    sh[threadIdx.x] = acc;
-    __syncthreads();
-    for (int s = THREADS / 2; s > 0; s >>= 1) {
-        if ((int)threadIdx.x < s) {
-            typename C::pt a = sh[threadIdx.x];
-            C::add(a, sh[threadIdx.x + s]);
-            sh[threadIdx.x] = a;
-        }
-        __syncthreads();
-    }
-    acc = sh[0];
-}
-
 // Most cut buckets hold a handful of partial sums (a bucket a few times over the task size): one thread each.
 template <class C>
 __global__ void __launch_bounds__(128)
@@ -485,6 +486,8 @@ msm_window_sum_kernel(const typename C::pt* __restrict__ a0, uint32_t n0, const 
     }
 }
 
+#endif  // G16_MSM_INSTANTIATE
+
 // bit i of mask = base i is the all-zero record (infinity)
 template <class C>
 __global__ void msm_inf_mask_kernel(const typename C::aff* __restrict__ bases, uint32_t n, uint32_t* __restrict__ mask) {
@@ -542,56 +545,7 @@ public:
     }
 
     // capacity for n points
-    void reserve(size_t n, const MsmConfig& cfg_in = MsmConfig()) {
-        cfg = cfg_in;
-        cap_n = n;
-        c = cfg.c ? cfg.c : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
-        if (c < 2) c = 2;
-        if (c > 24) c = 24;
-        W = msm_num_windows(c);
-        bpw = 1u << (c - 1);
-        nb = uint32_t(W) * bpw;
-        size_t m_max = n * size_t(W);
-        if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
-        // level-0 chunks: 16 buckets when there are enough buckets to fill the machine with chunk threads, else 8
-        // (half the dependency chain); level 1 works on bpw/L points only, so its chunks are short (latency, not work)
-        L = cfg.L ? cfg.L : (nb >= (2u << 20) ? 16 : 8);
-        L1 = 4;
-        cpw = (bpw + L - 1) / L;
-        int dev = 0, sms = 148;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        slots = size_t(sms) * (sizeof(pt) > 128 ? 512 : 1024);
-        size_t e = m_max ? m_max : 1;
-        keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_a.alloc(e * 4); vals_b.alloc(e * 4);
-        start.alloc(size_t(nb) * 4); end.alloc(size_t(nb) * 4);
-        ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4); nblk.alloc(size_t(nb + 1) * 4);
-        task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
-        cut_list.alloc((m_max / T_MIN + 2) * 4);  // a cut bucket holds more than T >= T_MIN entries
-        buckets.alloc(size_t(nb) * sizeof(pt));
-        cpw1 = (cpw + L1 - 1) / L1;
-        chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
-        chunk_sum.alloc(size_t(W) * cpw * sizeof(pt));
-        chunk2_out.alloc(size_t(W) * cpw1 * sizeof(pt));
-        slice_out.alloc(size_t(W) * SUM_SLICES * sizeof(pt));
-        window_out.alloc(size_t(W) * sizeof(pt));
-        counters.alloc(64);
-        size_t t1 = 0, t3 = 0;
-        cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
-        cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
-        cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)e, 0, key_bits());
-        cub::DeviceScan::ExclusiveSum(nullptr, t3, ntasks.as<uint32_t>(), task_base.as<uint32_t>(), (int)(nb + 1));
-        cub_tmp.alloc((t1 > t3 ? t1 : t3) + 256);
-        if (!h_counters) G16_CUDA(cudaMallocHost(&h_counters, 64));
-        if (!h_windows) G16_CUDA(cudaMallocHost(&h_windows, 32 * sizeof(pt) * 8));
-        if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
-        if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
-        if (!ev_acc1) G16_CUDA(cudaEventCreate(&ev_acc1));
-        if (!ev_mrg0) G16_CUDA(cudaEventCreate(&ev_mrg0));
-        if (!ev_mrg1) G16_CUDA(cudaEventCreate(&ev_mrg1));
-        for (auto& e : ev_t)
-            if (!e) G16_CUDA(cudaEventCreate(&e));
-    }
+    void reserve(size_t n, const MsmConfig& cfg_in = MsmConfig());
 
     // timeline of the last run relative to `base` (an event recorded earlier), milliseconds:
     // [0] start, [1] digits done, [2] sort + task counts done, [3] accumulate starts, [4] accumulate done, [5] window sums on the host
@@ -614,179 +568,16 @@ public:
     }
 
     // stage 1: digits (async).  scalars/bases/mask are device pointers; n <= reserved capacity.
-    void stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
-        if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
-        bases = bases_;
-        n = n_;
-        stream = s;
-        G16_CUDA(cudaEventRecord(ev_t[0], s));
-        G16_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
-        if (n) {
-            msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, W,
-                                                                          keys_a.as<uint32_t>(), vals_a.as<uint32_t>(),
-                                                                          counters.as<unsigned long long>());
-            G16_CUDA(cudaGetLastError());
-            G16_LAUNCHED(1);
-        }
-        acc_timed = false;
-        G16_CUDA(cudaEventRecord(ev_t[1], s));
-        G16_CUDA(cudaMemcpyAsync(h_counters, counters.p, 16, cudaMemcpyDeviceToHost, s));
-    }
+    void stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s);
 
     // stage 2: sort + task counts (reads the entry count -> one stream sync)
-    void stage2() {
-        cudaStream_t s = stream;
-        G16_CUDA(cudaStreamSynchronize(s));
-        m = (size_t)h_counters[0];
-        T = cfg.T;
-        if (T == 0) {
-            // enough tasks to fill the machine several times over: a task is one thread's dependency chain, so its
-            // length bounds the kernel's tail; a cut bucket costs one extra full addition per task
-            size_t t = (merge_enabled() ? m / 2 : m) / slots;
-            T = uint32_t(t < T_MIN ? T_MIN : t > T_MAX ? T_MAX : t);
-        }
-        if (T < T_MIN) T = T_MIN;
-        stats = MsmStats();
-        stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb; stats.T = T;
-        G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
-        if (m == 0) {
-            G16_CUDA(cudaEventRecord(ev_t[2], s));
-            return;
-        }
-        cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
-        cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
-        size_t tb = cub_tmp.bytes;
-        G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, dk, dv, (int)m, 0, key_bits(), s));
-        sorted_keys = dk.Current();
-        sorted_vals = dv.Current();
-        G16_CUDA(cudaMemsetAsync(start.p, 0, size_t(nb) * 4, s));
-        G16_CUDA(cudaMemsetAsync(end.p, 0, size_t(nb) * 4, s));
-        msm_bounds_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s>>>(sorted_keys, (uint32_t)m, start.as<uint32_t>(),
-                                                                      end.as<uint32_t>());
-        merged_slots = 0;
-        if (merge_enabled() && m >= merge_min() && ((m + 1) / 2) * (sizeof(aff) + sizeof(fe)) <= (size_t(24) << 30)) {
-            // one round of batched-affine pair additions in front of the accumulation (see msm_pair_merge_kernel)
-            uint32_t nslots = uint32_t((m + 1) / 2);
-            grow(merged, size_t(nslots) * sizeof(aff));
-            grow(prefix, size_t(nslots) * sizeof(fe));
-            uint32_t want = uint32_t(slots / 2);                 // threads that fill the machine
-            uint32_t per = (nslots + want - 1) / want;
-            per = per < 32 ? 32 : per > 256 ? 256 : per;         // slots per thread = the inversion's batch
-            uint32_t blocks = ((nslots + per - 1) / per + 127) / 128;
-            per = (nslots + blocks * 128 - 1) / (blocks * 128);
-            G16_CUDA(cudaEventRecord(ev_mrg0, s));
-            msm_pair_merge_kernel<C><<<blocks, 128, 0, s>>>(bases, sorted_keys, sorted_vals, start.as<uint32_t>(), (uint32_t)m,
-                                                            nslots, per, prefix.as<fe>(), merged.as<aff>(), dv.Alternate());
-            G16_CUDA(cudaEventRecord(ev_mrg1, s));
-            msm_merged_end_kernel<<<(nb + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb);
-            G16_CUDA(cudaGetLastError());
-            G16_LAUNCHED(2);
-            sorted_vals = dv.Alternate();
-            merged_slots = nslots;
-        }
-        uint32_t* cut_count = counters.as<uint32_t>() + 4;  // byte offset 16
-        msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb, T,
-                                                                    ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
-                                                                    nblk.as<uint32_t>(), cut_list.as<uint32_t>(), cut_count);
-        G16_LAUNCHED(2);
-        uint32_t* src[3] = {ntasks.as<uint32_t>(), nparts.as<uint32_t>(), nblk.as<uint32_t>()};
-        uint32_t* dst[3] = {task_base.as<uint32_t>(), part_base.as<uint32_t>(), blk_base.as<uint32_t>()};
-        uint32_t* h32 = reinterpret_cast<uint32_t*>(h_counters);
-        for (int i = 0; i < 3; i++) {
-            tb = cub_tmp.bytes;
-            G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, src[i], dst[i], (int)(nb + 1), s));
-            // h32[4] = tasks, [5] = partial sums, [6] = combine blocks, [7] = cut buckets
-            G16_CUDA(cudaMemcpyAsync(h32 + 4 + i, dst[i] + nb, 4, cudaMemcpyDeviceToHost, s));
-        }
-        G16_CUDA(cudaMemcpyAsync(h32 + 7, cut_count, 4, cudaMemcpyDeviceToHost, s));
-        G16_CUDA(cudaEventRecord(ev_t[2], s));
-    }
+    void stage2();
 
     // stage 3: accumulate + reductions (reads the task count -> one stream sync); window sums go to the host.
     // `s3` (optional) = a different stream for this stage: the prover keeps the H MSM's digits + sort on the
     // high-priority transform stream (so the sort is not starved by the witness MSMs' accumulations) and its
     // accumulation on the lowest-priority stream (so it fills the machine under everything else).
-    void stage3(cudaStream_t s3 = nullptr) {
-        cudaStream_t s = s3 ? s3 : stream;
-        if (s != stream) G16_CUDA(cudaStreamWaitEvent(s, ev_t[2], 0));
-        if (m != 0) {
-            G16_CUDA(cudaStreamSynchronize(stream));
-            const uint32_t* h32 = reinterpret_cast<const uint32_t*>(h_counters);
-            uint32_t nt = h32[4], np = h32[5], nblocks = h32[6], ncut = h32[7];
-            stats.tasks = nt;
-            stats.cut_buckets = ncut;
-            // the stream is idle here, so growing these is safe
-            grow(t_begin, size_t(nt) * 4); grow(t_len, size_t(nt) * 4); grow(t_out, size_t(nt) * 4);
-            grow(tk_a, size_t(nt) * 4); grow(tk_b, size_t(nt) * 4); grow(tv_a, size_t(nt) * 4); grow(tv_b, size_t(nt) * 4);
-            grow(parts, size_t(np) * sizeof(pt));
-            grow(parts2, size_t(nblocks) * sizeof(pt));
-            cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
-            cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
-            int bits = 1;
-            while ((1u << bits) <= T) bits++;
-            size_t need = 0;
-            cub::DeviceRadixSort::SortPairs(nullptr, need, tk, tv, (int)nt, 0, bits);
-            grow(task_tmp, need + 256);
-            msm_make_tasks_kernel<<<(nt + 255) / 256, 256, 0, s>>>(
-                start.as<uint32_t>(), end.as<uint32_t>(), task_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, nt, T,
-                t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), tk_a.as<uint32_t>(),
-                tv_a.as<uint32_t>());
-            size_t tb = task_tmp.bytes;
-            G16_CUDA(cub::DeviceRadixSort::SortPairs(task_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
-            G16_CUDA(cudaEventRecord(ev_acc0, s));
-            bool launched = false;
-            if constexpr (sizeof(pt) <= 128) {
-                if (acc_minb() == 4) {
-                    msm_accumulate_kernel<C, 4><<<(nt + 127) / 128, 128, 0, s>>>(
-                        bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(),
-                        nt, buckets.as<pt>(), parts.as<pt>());
-                    launched = true;
-                }
-            }
-            if (!launched)
-                msm_accumulate_kernel<C, 1><<<(nt + 127) / 128, 128, 0, s>>>(
-                    bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
-                    buckets.as<pt>(), parts.as<pt>());
-            G16_CUDA(cudaEventRecord(ev_acc1, s));
-            acc_timed = true;
-            G16_CUDA(cudaGetLastError());
-            G16_LAUNCHED(2);
-            if (ncut) {
-                msm_combine_small_kernel<C><<<(ncut + 127) / 128, 128, 0, s>>>(
-                    cut_list.as<uint32_t>(), ncut, part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
-                G16_LAUNCHED(1);
-                if (nblocks) {
-                    msm_combine1_kernel<C, RED_THREADS><<<nblocks, RED_THREADS, 0, s>>>(
-                        blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, parts.as<pt>(), parts2.as<pt>());
-                    msm_combine2_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
-                        cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), parts2.as<pt>(), buckets.as<pt>());
-                    G16_LAUNCHED(2);
-                }
-                G16_CUDA(cudaGetLastError());
-            }
-        }
-        uint32_t nchunks = uint32_t(W) * cpw, nchunks1 = uint32_t(W) * cpw1;
-        msm_chunk_reduce_kernel<C, true, false><<<(nchunks + 63) / 64, 64, 0, s>>>(
-            buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
-        msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
-            chunk_sum.as<pt>(), cpw, L1, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
-        const pt* a0 = chunk_out.as<pt>();
-        uint32_t n0 = cpw;
-        if (cpw >= 32 * SUM_SLICES) {  // long windows: sum the level-0 results in slices first (short dependency chains)
-            msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * SUM_SLICES, RED_THREADS, 0, s>>>(
-                chunk_out.as<pt>(), cpw, SUM_SLICES, slice_out.as<pt>());
-            a0 = slice_out.as<pt>();
-            n0 = SUM_SLICES;
-            G16_LAUNCHED(1);
-        }
-        msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(a0, n0, chunk2_out.as<pt>(), cpw1, L,
-                                                                        window_out.as<pt>());
-        G16_CUDA(cudaGetLastError());
-        G16_LAUNCHED(3);
-        G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));
-        G16_CUDA(cudaEventRecord(ev_t[3], s));
-        stream = s;
-    }
+    void stage3(cudaStream_t s3 = nullptr);
 
     // whole MSM on one stream; returns after the window sums are in host memory
     void run(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
@@ -857,6 +648,233 @@ private:
     cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr, ev_t[4] = {nullptr, nullptr, nullptr, nullptr};
     bool acc_timed = false;
 };
+
+#ifdef G16_MSM_INSTANTIATE
+// ---- out-of-class definitions: compiled in msm.cu only, so that the kernels exist once in the library
+template <class C>
+void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
+    cfg = cfg_in;
+    cap_n = n;
+    c = cfg.c ? cfg.c : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
+    if (c < 2) c = 2;
+    if (c > 24) c = 24;
+    W = msm_num_windows(c);
+    bpw = 1u << (c - 1);
+    nb = uint32_t(W) * bpw;
+    size_t m_max = n * size_t(W);
+    if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
+    // level-0 chunks: 16 buckets when there are enough buckets to fill the machine with chunk threads, else 8
+    // (half the dependency chain); level 1 works on bpw/L points only, so its chunks are short (latency, not work)
+    L = cfg.L ? cfg.L : (nb >= (2u << 20) ? 16 : 8);
+    L1 = 4;
+    cpw = (bpw + L - 1) / L;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    slots = size_t(sms) * (sizeof(pt) > 128 ? 512 : 1024);
+    size_t e = m_max ? m_max : 1;
+    keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_a.alloc(e * 4); vals_b.alloc(e * 4);
+    start.alloc(size_t(nb) * 4); end.alloc(size_t(nb) * 4);
+    ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4); nblk.alloc(size_t(nb + 1) * 4);
+    task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
+    cut_list.alloc((m_max / T_MIN + 2) * 4);  // a cut bucket holds more than T >= T_MIN entries
+    buckets.alloc(size_t(nb) * sizeof(pt));
+    cpw1 = (cpw + L1 - 1) / L1;
+    chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
+    chunk_sum.alloc(size_t(W) * cpw * sizeof(pt));
+    chunk2_out.alloc(size_t(W) * cpw1 * sizeof(pt));
+    slice_out.alloc(size_t(W) * SUM_SLICES * sizeof(pt));
+    window_out.alloc(size_t(W) * sizeof(pt));
+    counters.alloc(64);
+    size_t t1 = 0, t3 = 0;
+    cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
+    cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
+    cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)e, 0, key_bits());
+    cub::DeviceScan::ExclusiveSum(nullptr, t3, ntasks.as<uint32_t>(), task_base.as<uint32_t>(), (int)(nb + 1));
+    cub_tmp.alloc((t1 > t3 ? t1 : t3) + 256);
+    if (!h_counters) G16_CUDA(cudaMallocHost(&h_counters, 64));
+    if (!h_windows) G16_CUDA(cudaMallocHost(&h_windows, 32 * sizeof(pt) * 8));
+    if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
+    if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
+    if (!ev_acc1) G16_CUDA(cudaEventCreate(&ev_acc1));
+    if (!ev_mrg0) G16_CUDA(cudaEventCreate(&ev_mrg0));
+    if (!ev_mrg1) G16_CUDA(cudaEventCreate(&ev_mrg1));
+    for (auto& e : ev_t)
+        if (!e) G16_CUDA(cudaEventCreate(&e));
+}
+
+template <class C>
+void Msm<C>::stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
+    if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
+    bases = bases_;
+    n = n_;
+    stream = s;
+    G16_CUDA(cudaEventRecord(ev_t[0], s));
+    G16_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
+    if (n) {
+        msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, W,
+                                                                      keys_a.as<uint32_t>(), vals_a.as<uint32_t>(),
+                                                                      counters.as<unsigned long long>());
+        G16_CUDA(cudaGetLastError());
+        G16_LAUNCHED(1);
+    }
+    acc_timed = false;
+    G16_CUDA(cudaEventRecord(ev_t[1], s));
+    G16_CUDA(cudaMemcpyAsync(h_counters, counters.p, 16, cudaMemcpyDeviceToHost, s));
+}
+
+template <class C>
+void Msm<C>::stage2() {
+    cudaStream_t s = stream;
+    G16_CUDA(cudaStreamSynchronize(s));
+    m = (size_t)h_counters[0];
+    T = cfg.T;
+    if (T == 0) {
+        // enough tasks to fill the machine several times over: a task is one thread's dependency chain, so its
+        // length bounds the kernel's tail; a cut bucket costs one extra full addition per task
+        size_t t = (merge_enabled() ? m / 2 : m) / slots;
+        T = uint32_t(t < T_MIN ? T_MIN : t > T_MAX ? T_MAX : t);
+    }
+    if (T < T_MIN) T = T_MIN;
+    stats = MsmStats();
+    stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb; stats.T = T;
+    G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
+    if (m == 0) {
+        G16_CUDA(cudaEventRecord(ev_t[2], s));
+        return;
+    }
+    cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
+    cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
+    size_t tb = cub_tmp.bytes;
+    G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, dk, dv, (int)m, 0, key_bits(), s));
+    sorted_keys = dk.Current();
+    sorted_vals = dv.Current();
+    G16_CUDA(cudaMemsetAsync(start.p, 0, size_t(nb) * 4, s));
+    G16_CUDA(cudaMemsetAsync(end.p, 0, size_t(nb) * 4, s));
+    msm_bounds_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s>>>(sorted_keys, (uint32_t)m, start.as<uint32_t>(),
+                                                                  end.as<uint32_t>());
+    merged_slots = 0;
+    if (merge_enabled() && m >= merge_min() && ((m + 1) / 2) * (sizeof(aff) + sizeof(fe)) <= (size_t(24) << 30)) {
+        // one round of batched-affine pair additions in front of the accumulation (see msm_pair_merge_kernel)
+        uint32_t nslots = uint32_t((m + 1) / 2);
+        grow(merged, size_t(nslots) * sizeof(aff));
+        grow(prefix, size_t(nslots) * sizeof(fe));
+        uint32_t want = uint32_t(slots / 2);                 // threads that fill the machine
+        uint32_t per = (nslots + want - 1) / want;
+        per = per < 32 ? 32 : per > 256 ? 256 : per;         // slots per thread = the inversion's batch
+        uint32_t blocks = ((nslots + per - 1) / per + 127) / 128;
+        per = (nslots + blocks * 128 - 1) / (blocks * 128);
+        G16_CUDA(cudaEventRecord(ev_mrg0, s));
+        msm_pair_merge_kernel<C><<<blocks, 128, 0, s>>>(bases, sorted_keys, sorted_vals, start.as<uint32_t>(), (uint32_t)m,
+                                                        nslots, per, prefix.as<fe>(), merged.as<aff>(), dv.Alternate());
+        G16_CUDA(cudaEventRecord(ev_mrg1, s));
+        msm_merged_end_kernel<<<(nb + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb);
+        G16_CUDA(cudaGetLastError());
+        G16_LAUNCHED(2);
+        sorted_vals = dv.Alternate();
+        merged_slots = nslots;
+    }
+    uint32_t* cut_count = counters.as<uint32_t>() + 4;  // byte offset 16
+    msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb, T,
+                                                                ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
+                                                                nblk.as<uint32_t>(), cut_list.as<uint32_t>(), cut_count);
+    G16_LAUNCHED(2);
+    uint32_t* src[3] = {ntasks.as<uint32_t>(), nparts.as<uint32_t>(), nblk.as<uint32_t>()};
+    uint32_t* dst[3] = {task_base.as<uint32_t>(), part_base.as<uint32_t>(), blk_base.as<uint32_t>()};
+    uint32_t* h32 = reinterpret_cast<uint32_t*>(h_counters);
+    for (int i = 0; i < 3; i++) {
+        tb = cub_tmp.bytes;
+        G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, src[i], dst[i], (int)(nb + 1), s));
+        // h32[4] = tasks, [5] = partial sums, [6] = combine blocks, [7] = cut buckets
+        G16_CUDA(cudaMemcpyAsync(h32 + 4 + i, dst[i] + nb, 4, cudaMemcpyDeviceToHost, s));
+    }
+    G16_CUDA(cudaMemcpyAsync(h32 + 7, cut_count, 4, cudaMemcpyDeviceToHost, s));
+    G16_CUDA(cudaEventRecord(ev_t[2], s));
+}
+
+template <class C>
+void Msm<C>::stage3(cudaStream_t s3) {
+    cudaStream_t s = s3 ? s3 : stream;
+    if (s != stream) G16_CUDA(cudaStreamWaitEvent(s, ev_t[2], 0));
+    if (m != 0) {
+        G16_CUDA(cudaStreamSynchronize(stream));
+        const uint32_t* h32 = reinterpret_cast<const uint32_t*>(h_counters);
+        uint32_t nt = h32[4], np = h32[5], nblocks = h32[6], ncut = h32[7];
+        stats.tasks = nt;
+        stats.cut_buckets = ncut;
+        // the stream is idle here, so growing these is safe
+        grow(t_begin, size_t(nt) * 4); grow(t_len, size_t(nt) * 4); grow(t_out, size_t(nt) * 4);
+        grow(tk_a, size_t(nt) * 4); grow(tk_b, size_t(nt) * 4); grow(tv_a, size_t(nt) * 4); grow(tv_b, size_t(nt) * 4);
+        grow(parts, size_t(np) * sizeof(pt));
+        grow(parts2, size_t(nblocks) * sizeof(pt));
+        cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
+        cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
+        int bits = 1;
+        while ((1u << bits) <= T) bits++;
+        size_t need = 0;
+        cub::DeviceRadixSort::SortPairs(nullptr, need, tk, tv, (int)nt, 0, bits);
+        grow(task_tmp, need + 256);
+        msm_make_tasks_kernel<<<(nt + 255) / 256, 256, 0, s>>>(
+            start.as<uint32_t>(), end.as<uint32_t>(), task_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, nt, T,
+            t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), tk_a.as<uint32_t>(),
+            tv_a.as<uint32_t>());
+        size_t tb = task_tmp.bytes;
+        G16_CUDA(cub::DeviceRadixSort::SortPairs(task_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
+        G16_CUDA(cudaEventRecord(ev_acc0, s));
+        bool launched = false;
+        if constexpr (sizeof(pt) <= 128) {
+            if (acc_minb() == 4) {
+                msm_accumulate_kernel<C, 4><<<(nt + 127) / 128, 128, 0, s>>>(
+                    bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(),
+                    nt, buckets.as<pt>(), parts.as<pt>());
+                launched = true;
+            }
+        }
+        if (!launched)
+            msm_accumulate_kernel<C, 1><<<(nt + 127) / 128, 128, 0, s>>>(
+                bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
+                buckets.as<pt>(), parts.as<pt>());
+        G16_CUDA(cudaEventRecord(ev_acc1, s));
+        acc_timed = true;
+        G16_CUDA(cudaGetLastError());
+        G16_LAUNCHED(2);
+        if (ncut) {
+            msm_combine_small_kernel<C><<<(ncut + 127) / 128, 128, 0, s>>>(
+                cut_list.as<uint32_t>(), ncut, part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
+            G16_LAUNCHED(1);
+            if (nblocks) {
+                msm_combine1_kernel<C, RED_THREADS><<<nblocks, RED_THREADS, 0, s>>>(
+                    blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, parts.as<pt>(), parts2.as<pt>());
+                msm_combine2_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
+                    cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), parts2.as<pt>(), buckets.as<pt>());
+                G16_LAUNCHED(2);
+            }
+            G16_CUDA(cudaGetLastError());
+        }
+    }
+    uint32_t nchunks = uint32_t(W) * cpw, nchunks1 = uint32_t(W) * cpw1;
+    msm_chunk_reduce_kernel<C, true, false><<<(nchunks + 63) / 64, 64, 0, s>>>(
+        buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
+    msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
+        chunk_sum.as<pt>(), cpw, L1, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
+    const pt* a0 = chunk_out.as<pt>();
+    uint32_t n0 = cpw;
+    if (cpw >= 32 * SUM_SLICES) {  // long windows: sum the level-0 results in slices first (short dependency chains)
+        msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * SUM_SLICES, RED_THREADS, 0, s>>>(
+            chunk_out.as<pt>(), cpw, SUM_SLICES, slice_out.as<pt>());
+        a0 = slice_out.as<pt>();
+        n0 = SUM_SLICES;
+        G16_LAUNCHED(1);
+    }
+    msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(a0, n0, chunk2_out.as<pt>(), cpw1, L,
+                                                                    window_out.as<pt>());
+    G16_CUDA(cudaGetLastError());
+    G16_LAUNCHED(3);
+    G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));
+    G16_CUDA(cudaEventRecord(ev_t[3], s));
+    stream = s;
+}
+#endif  // G16_MSM_INSTANTIATE
 
 #ifndef G16_MSM_INSTANTIATE
 extern template class Msm<G1>;
