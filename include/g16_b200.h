@@ -92,6 +92,19 @@ int g16_h_transform(g16_zkey* zk, int which);
 int g16_h_buffer(g16_zkey* zk, int poly /*0 A, 1 B, 2 C*/, void** d_ptr, uint64_t* h_lo, uint64_t* h_n);
 int g16_prove_partial_joined(g16_zkey* zk, const void* d_a, const void* d_b, const void* d_c, uint8_t* partial_out);
 
+/* ---- verification: replaces `snarkjs groth16 verify <vkey.json> <public.json> <proof.json>`
+ * (scripts/g16_verify.sh:212-216), the consumer of the prover's output.  Host code only -- works without a GPU.
+ * Inputs are the JSON texts; *ok = 1 iff e(-A,B) e(alpha,beta) e(vk_x,gamma) e(C,delta) == 1 and every point is on
+ * its curve.  Returns G16_OK, or G16_ERR_FORMAT (message in g16_last_error) for malformed JSON. */
+int g16_verify(const char* vkey_json, size_t vkey_len, const char* public_json, size_t public_len,
+               const char* proof_json, size_t proof_len, int* ok);
+
+/* proof + vkey + public -> the text of sanitized_proof.json, the 43-bit x 6 limb input of the recursive verifier
+ * circuit incl. e(-alpha, beta): replaces scripts/sanitize_groth16_proof.py:39-123.  Host code only.  *out_len: in =
+ * capacity, out = length (G16_ERR_SHORT_BUFFER writes the needed size back). */
+int g16_sanitize(const char* vkey_json, size_t vkey_len, const char* public_json, size_t public_len,
+                 const char* proof_json, size_t proof_len, char* out, size_t* out_len);
+
 /* ---- operators on the path, usable on their own (metric: BN254 MSM Mpts/s; NTT GB/s) ------------------------
  * MSM: bases = zkey records (affine, Montgomery, all-zero = infinity; 64 B G1 / 128 B G2), scalars = 32 B standard
  * form.  *_host take host pointers (copies inside), *_dev take device pointers.  Result: affine, Montgomery,

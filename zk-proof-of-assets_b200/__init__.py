@@ -37,7 +37,7 @@ ABI_SYMBOLS = [
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
     "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace", "g16_h_transform", "g16_h_buffer",
-    "g16_prove_partial_joined",
+    "g16_prove_partial_joined", "g16_verify", "g16_sanitize",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -108,6 +108,10 @@ def lib():
         L.g16_h_transform.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.g16_h_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_prove_partial_joined.argtypes = [ctypes.c_void_p] * 5
+        L.g16_sanitize.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
+                                   ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_verify.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
+                                 ctypes.c_size_t, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -292,6 +296,37 @@ class groth16:
         with ZKey(zkey_file_name, device=device) as zk, open(wtns_file_name, "rb") as f:
             proof, public = zk.prove(f.read(), r=r, s=s, style=STYLE_SNARKJS)
         return json.loads(proof), json.loads(public)
+
+
+def verify(vkey, public_signals, proof):
+    """`snarkjs.groth16.verify(vkey, publicSignals, proof)` look-alike (scripts/g16_verify.sh:212-216): parsed JSON
+    objects or JSON texts in, bool out.  Native host code (csrc/verify*.hpp), no GPU needed."""
+    def text(x):
+        if isinstance(x, (bytes, bytearray)):
+            return bytes(x)
+        return (x if isinstance(x, str) else json.dumps(x)).encode()
+    v, u, p = text(vkey), text(public_signals), text(proof)
+    ok = ctypes.c_int(0)
+    _check(lib().g16_verify(v, len(v), u, len(u), p, len(p), ctypes.byref(ok)))
+    return bool(ok.value)
+
+
+def sanitize(vkey, public_signals, proof):
+    """scripts/sanitize_groth16_proof.py as one call: -> the text of sanitized_proof.json (Python json.dump layout)"""
+    def text(x):
+        if isinstance(x, (bytes, bytearray)):
+            return bytes(x)
+        return (x if isinstance(x, str) else json.dumps(x)).encode()
+    v, u, p = text(vkey), text(public_signals), text(proof)
+    n = ctypes.c_size_t(1 << 16)
+    buf = ctypes.create_string_buffer(n.value)
+    rc = lib().g16_sanitize(v, len(v), u, len(u), p, len(p), buf, ctypes.byref(n))
+    if rc == G16_ERR_SHORT_BUFFER:
+        buf = ctypes.create_string_buffer(n.value + 1)
+        n = ctypes.c_size_t(len(buf))
+        rc = lib().g16_sanitize(v, len(v), u, len(u), p, len(p), buf, ctypes.byref(n))
+    _check(rc)
+    return buf.raw[:n.value].decode()
 
 
 def prove_files(zkey_path, wtns_path, proof_path, public_path, r=None, s=None, style=STYLE_RAPIDSNARK, device=-1):

@@ -9,6 +9,10 @@
 // Service mode (not part of the reference's contract, see csrc/service.hpp):
 //     prover --serve [--socket PATH] [--devices 0,1,...] [--max-keys N]
 //     prover --ping | --stats | --shutdown          (socket from --socket or G16_SERVICE)
+// Verification (the argv of `snarkjs groth16 verify`, scripts/g16_verify.sh:212-216; no GPU needed):
+//     prover --verify <verification_key.json> <public.json> <proof.json>     exit 0 + "OK!" | exit 1 + "Invalid proof"
+//     prover --sanitize <verification_key.json> <public.json> <proof.json> <sanitized_proof.json>
+//                                   the limb file scripts/sanitize_groth16_proof.py:112-123 writes, byte for byte
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
@@ -69,7 +73,45 @@ static int control(int argc, char** argv) {
     return reply.compare(0, 2, "OK") == 0 ? 0 : 1;
 }
 
+static int verify_cli(int argc, char** argv) {
+    const bool sanitize = !std::strcmp(argv[1], "--sanitize");
+    if (argc != (sanitize ? 6 : 5)) {
+        std::fprintf(stderr, "Usage: prover --verify <verification_key.json> <public.json> <proof.json>\n"
+                             "       prover --sanitize <verification_key.json> <public.json> <proof.json> <sanitized_proof.json>\n");
+        return 1;
+    }
+    std::vector<uint8_t> f[3];
+    std::string err;
+    for (int i = 0; i < 3; i++)
+        if (!g16svc::read_file(argv[2 + i], f[i], err)) {
+            std::fprintf(stderr, "prover: %s\n", err.c_str());
+            return 1;
+        }
+    if (sanitize) {
+        std::vector<char> out(1 << 20);
+        size_t n = out.size();
+        int rc = g16_sanitize((const char*)f[0].data(), f[0].size(), (const char*)f[1].data(), f[1].size(),
+                              (const char*)f[2].data(), f[2].size(), out.data(), &n);
+        if (rc != G16_OK || !g16svc::write_file(argv[5], out.data(), n, err)) {
+            std::fprintf(stderr, "prover: %s\n", rc != G16_OK ? g16_last_error() : err.c_str());
+            return rc != G16_OK ? rc : 1;
+        }
+        return 0;
+    }
+    int ok = 0;
+    int rc = g16_verify((const char*)f[0].data(), f[0].size(), (const char*)f[1].data(), f[1].size(),
+                        (const char*)f[2].data(), f[2].size(), &ok);
+    if (rc != G16_OK) {
+        std::fprintf(stderr, "prover: %s\n", g16_last_error());
+        return rc;
+    }
+    if (ok) std::printf("OK!\n");
+    else std::fprintf(stderr, "Invalid proof\n");
+    return ok ? 0 : 1;
+}
+
 int main(int argc, char** argv) {
+    if (argc >= 2 && (!std::strcmp(argv[1], "--verify") || !std::strcmp(argv[1], "--sanitize"))) return verify_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--serve") || !std::strcmp(argv[1], "--ping") ||
                       !std::strcmp(argv[1], "--stats") || !std::strcmp(argv[1], "--shutdown")))
         return control(argc, argv);
