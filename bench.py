@@ -141,6 +141,9 @@ G2_MADD_MODMULS = 28      # the same over Fq2: 8 x 3 (Karatsuba) + 2 x 2
 NTT_BYTES_PER_POINT = 384  # H pipeline, strict: 6 transforms x (32 B read + 32 B write) per domain point
 
 
+H_TABLE = {"auto": 0, "on": 1, "off": -1}
+
+
 def measured_traffic(workload):
     """dram bytes from the committed ncu --set full capture of this workload (profiles/traffic.json), or {}"""
     try:
@@ -192,9 +195,9 @@ def run_b200(args):
     shard = args.mode in ("shard", "shard-rep") and world > 1
     dist_ntt = args.mode == "shard"     # coset transforms spread over the ranks too (one all-to-all per polynomial)
     if shard:
-        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, shard_rank=rank, shard_count=world)
+        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, shard_rank=rank, shard_count=world, h_table=H_TABLE[args.h_table])
     else:
-        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c)
+        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, h_table=H_TABLE[args.h_table])
     t_open = time.perf_counter() - t_open
     zkey_len = len(zkey)
     del zkey
@@ -292,6 +295,13 @@ def run_b200(args):
     if rank == 0:
         peaks = measured_peaks()
         traffic = measured_traffic(args.workload)
+        # the H section's fixed-base window table (opts.h_table): one bucket set of c+4-bit windows; told apart from the
+        # plain launch by the window width the run reports
+        plain_c = max(6, min(20, zk.domain_size.bit_length() - 1 - 5))     # msm_pick_c (csrc/msm.cuh)
+        h_tabled = not args.msm_c and stats["H"]["c"] > plain_c
+        if not h_tabled and "msm_accumulate_H_plain" in traffic:
+            traffic = dict(traffic, msm_accumulate_H=traffic["msm_accumulate_H_plain"])
+            traffic.pop("msm_accumulate", None)
         acc_alg_bytes = 68 * g1_adds + 132 * g2_adds      # one base record + one 4-byte entry per mixed addition
         h_ms = acc_ms["H"] / steps
         h_ops = MODMUL_OPS * G1_MADD_MODMULS * stats["H"]["additions"]
@@ -306,6 +316,7 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "u32 limbs (256-bit Montgomery Fr/Fq/Fq2)", "data": "synthetic",
             "config": {"workload": args.workload, "description": desc, "n_vars": nv, "n_public": npub,
                        "n_constraints": ncons, "domain_size": zk.domain_size, "n_coefs": zk.n_coefs,
+                       "h_window_table": h_tabled,
                        "zkey_bytes": zkey_len, "proofs_per_step": jobs,
                        "parallelism": ("base-range shards x%d, %s, NCCL all-gather of 768 B partials"
                                        % (world, "A/B/C transforms on ranks 0-%d + all-to-all of slices" % (min(world, 3) - 1)
@@ -442,6 +453,8 @@ def main():
                          "ranks 0-2 with an all-to-all of their slices, one all-gather of partial sums; shard-rep = the "
                          "same with the transforms repeated on every rank (no slice exchange)")
     ap.add_argument("--msm-c", type=int, default=0, help="Pippenger window bits (0 = automatic)")
+    ap.add_argument("--h-table", default="auto", choices=sorted(H_TABLE),
+                    help="fixed-base window table for the H section (auto = on when it fits in a quarter of free HBM)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", dest="verify", action="store_false")
     ap.add_argument("--cpu-budget", type=float, default=25.0, help="seconds of CPU work for the cpu_baseline leg")

@@ -44,7 +44,9 @@ typedef struct {
     int32_t msm_c;       /* Pippenger window bits, 0 = automatic */
     int32_t shard_rank;  /* base-range sharding of every MSM across GPUs: this handle holds slice rank/count */
     int32_t shard_count; /* 0 or 1 = whole key */
-    int32_t reserved[8];
+    int32_t h_table;     /* fixed-base window table for the H section (rows 2^(c w) * H_i, built at open):
+                            0 = automatic, 1 = always, -1 = never */
+    int32_t reserved[7];
 } g16_opts;
 
 void g16_opts_default(g16_opts* o);

@@ -410,6 +410,39 @@ def test_prove_closed_form_at_scale(pkg, n_vars, n_public, n_cons):
         assert st["H"]["additions"] > 0 and st["B2"]["additions"] > 0
 
 
+@pytest.mark.parametrize("msm_c", [0, 6, 9, 13])
+def test_prove_with_h_window_table_bit_exact(pkg, small_fixture, msm_c):
+    """opts.h_table = 1: the H MSM runs over the fixed-base window table (rows 2^(c w) * H_i, one bucket set);
+    the proof bytes must not change.  msm_c sweeps the table's row count (43, 29, 20 rows)."""
+    f = small_fixture
+    r, s = (R - 1), 0x1234567 << 190
+    want = g16.prove(f["zk"], f["w"], r, s)
+    with pkg.ZKey(bytes(f["zkey_bytes"]), msm_c=msm_c, h_table=1) as zk:
+        assert zk.prove(bytes(f["wtns_bytes"]), r=r, s=s) == want
+        assert zk.prove(bytes(f["wtns_bytes"]), r=r, s=s) == want      # the table is reused, not rebuilt
+    # sharded: each shard tabulates its own slice of section 9
+    partials = b""
+    handles = [pkg.ZKey(bytes(f["zkey_bytes"]), shard_rank=k, shard_count=2, msm_c=msm_c, h_table=1) for k in range(2)]
+    for h in handles:
+        h.load_witness(bytes(f["wtns_bytes"]))
+        partials += h.prove_partial()
+    assert handles[0].combine(partials, r=r, s=s) == want
+    for h in handles:
+        h.close()
+
+
+def test_prove_closed_form_at_scale_with_h_window_table(pkg):
+    sy = pkg.Synth(200000, 13, 262130, 11, 12)
+    zkey, wtns = sy.write()
+    r, s = 0xABCDEF0123456789 << 64, 0x1F2E3D4C5B6A7988 << 128
+    with pkg.ZKey(zkey, h_table=1) as zk, pkg.ZKey(zkey, h_table=-1) as plain:
+        proof, public = zk.prove(wtns, r=r, s=s)
+        assert json.loads(proof) == g16.proof_object(*sy.expected(r, s))
+        assert plain.prove(wtns, r=r, s=s) == (proof, public)
+        a, b = zk.msm_stats()["H"], plain.msm_stats()["H"]
+        assert a["additions"] < b["additions"] and a["c"] > b["c"]      # wider windows: fewer mixed additions
+
+
 SHARD_WORKER = r'''
 import os, sys, json
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))

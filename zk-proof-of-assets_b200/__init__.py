@@ -56,7 +56,8 @@ class Opts(ctypes.Structure):
     _fields_ = [
         ("device", ctypes.c_int32), ("style", ctypes.c_int32), ("has_rs", ctypes.c_int32),
         ("r", ctypes.c_uint8 * 32), ("s", ctypes.c_uint8 * 32), ("msm_c", ctypes.c_int32),
-        ("shard_rank", ctypes.c_int32), ("shard_count", ctypes.c_int32), ("reserved", ctypes.c_int32 * 8),
+        ("shard_rank", ctypes.c_int32), ("shard_count", ctypes.c_int32), ("h_table", ctypes.c_int32),
+        ("reserved", ctypes.c_int32 * 7),
     ]
 
 
@@ -141,10 +142,11 @@ def _check(rc):
         raise G16Error(rc, lib().g16_last_error().decode("utf-8", "replace"))
 
 
-def make_opts(device=-1, style=STYLE_RAPIDSNARK, r=None, s=None, msm_c=0, shard_rank=0, shard_count=1):
+def make_opts(device=-1, style=STYLE_RAPIDSNARK, r=None, s=None, msm_c=0, shard_rank=0, shard_count=1, h_table=0):
     o = Opts()
     lib().g16_opts_default(ctypes.byref(o))
     o.device, o.style, o.msm_c, o.shard_rank, o.shard_count = device, style, msm_c, shard_rank, shard_count
+    o.h_table = h_table
     if (r is None) != (s is None):
         raise ValueError("pin both r and s or neither")
     if r is not None:
@@ -171,9 +173,10 @@ class ZKey:
     """A proving key parsed once and kept resident on one GPU (g16_zkey_open).  Mirrors the role of the cached
     zkeys the workflow reuses across batches (scripts/full_workflow.sh:303-348)."""
 
-    def __init__(self, source, device=-1, msm_c=0, shard_rank=0, shard_count=1):
+    def __init__(self, source, device=-1, msm_c=0, shard_rank=0, shard_count=1, h_table=0):
+        """h_table: fixed-base window table for the H section (1 = always, -1 = never, 0 = automatic)"""
         self._h = ctypes.c_void_p()
-        self._opts = make_opts(device=device, msm_c=msm_c, shard_rank=shard_rank, shard_count=shard_count)
+        self._opts = make_opts(device=device, msm_c=msm_c, shard_rank=shard_rank, shard_count=shard_count, h_table=h_table)
         if isinstance(source, (str, os.PathLike)):
             _check(lib().g16_zkey_open(os.fsencode(source), ctypes.byref(self._opts), ctypes.byref(self._h)))
         else:

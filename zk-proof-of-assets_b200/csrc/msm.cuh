@@ -67,8 +67,10 @@ __device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
 // ---------------------------------------------------------------------------------------------------------
 // scalars: n x 8 u32 (standard form, < 2^254).  inf_mask: optional bitmask, bit i set = base i is infinity.
 static __global__ void msm_digits_kernel(const uint32_t* __restrict__ scalars, uint32_t n, const uint32_t* __restrict__ inf_mask,
-                                  int c, int W, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
+                                  int c, int W, uint32_t fold_n, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
                                   unsigned long long* __restrict__ counter) {
+    // fold_n != 0 (fixed-base window table, see msm_window_table_kernel): every window shares ONE bucket set and the
+    // entry points at row w of the table, base index w * fold_n + i, which holds 2^(c w) * base_i
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t half = 1u << (c - 1);
     const uint32_t mask = (1u << c) - 1;
@@ -118,9 +120,56 @@ static __global__ void msm_digits_kernel(const uint32_t* __restrict__ scalars, u
         if (d == 0 || d == (1u << c)) continue;
         uint32_t neg = carry;
         uint32_t mag = neg ? (1u << c) - d : d;  // 1 .. half
-        keys[pos] = (uint32_t)w * half + (mag - 1);
-        vals[pos] = i | (neg << 31);
+        keys[pos] = fold_n ? mag - 1 : (uint32_t)w * half + (mag - 1);
+        vals[pos] = (fold_n ? (uint32_t)w * fold_n + i : i) | (neg << 31);
         pos++;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// fixed-base window table (built once per key, for the H section whose scalars are dense)
+// ---------------------------------------------------------------------------------------------------------
+// table[w * n + i] = 2^(c w) * base_i in affine form, w = 0 .. Wd-1.  With it sum_i s_i B_i = sum_{i,w} d_{i,w} table[w][i]
+// is ONE bucket problem of 2^(c-1) buckets instead of Wd of them: c can be 4 bits wider for the same bucket count,
+// which removes ~20 % of the mixed additions, and the 255-doubling Horner chain at the end disappears.
+// One thread per base: Wd-1 runs of c doublings in XYZZ, then one shared inversion (prefix products of the ZZZ) to
+// bring the Wd-1 points back to affine: x = X (ZZ / ZZZ)^2, y = Y / ZZZ.
+constexpr int MSM_TABLE_MAX_W = 43;   // c >= 6
+template <class C>
+static __global__ void __launch_bounds__(128)
+msm_window_table_kernel(const typename C::aff* __restrict__ bases, uint32_t n, int c, int Wd, typename C::aff* __restrict__ table) {
+    typedef typename C::field F;
+    typedef typename C::fe fe;
+    typedef typename C::aff aff;
+    typedef typename C::pt pt;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    aff a = bases[i];
+    table[i] = a;
+    if (C::is_inf(a)) {
+        for (int w = 1; w < Wd; w++) table[size_t(w) * n + i] = a;
+        return;
+    }
+    fe zz[MSM_TABLE_MAX_W], zzz[MSM_TABLE_MAX_W], pre[MSM_TABLE_MAX_W];
+    pt q = C::from_affine(a);
+    fe prod = F::one();
+    for (int w = 1; w < Wd; w++) {
+        for (int k = 0; k < c; k++) q = C::dbl(q);
+        table[size_t(w) * n + i] = aff{q.x, q.y};   // numerators; divided below
+        zz[w] = q.zz;
+        zzz[w] = q.zzz;
+        pre[w] = prod;
+        prod = F::mul(prod, q.zzz);
+    }
+    fe inv = F::inv(prod);
+    for (int w = Wd - 1; w >= 1; w--) {
+        fe u = F::mul(inv, pre[w]);        // 1 / ZZZ_w
+        inv = F::mul(inv, zzz[w]);
+        fe zi = F::mul(u, zz[w]);          // 1 / Z_w
+        aff t = table[size_t(w) * n + i];
+        t.x = F::mul(t.x, F::sqr(zi));
+        t.y = F::mul(t.y, u);
+        table[size_t(w) * n + i] = t;
     }
 }
 
@@ -509,11 +558,22 @@ static inline int msm_pick_c_sparse(size_t n) {
     return c < 6 ? 6 : c;
 }
 
+// window width with a fixed-base table: 4 bits wider (one bucket set instead of W), then the narrowest width that
+// keeps the same number of table rows
+static inline int msm_pick_c_table(size_t n) {
+    int c = msm_pick_c(n) + 4;
+    if (c > 24) c = 24;
+    int W = msm_num_windows(c);
+    while (c > 6 && msm_num_windows(c - 1) == W) c--;
+    return c;
+}
+
 struct MsmConfig {
     bool sparse = false;  // scalars are witness-like (see msm_pick_c_sparse)
     int c = 0;          // window bits (0 = pick from n)
     uint32_t T = 0;     // max entries per task (0 = from the entry count: about 1024 tasks' worth of work per SM)
     uint32_t L = 0;     // buckets per reduction chunk (0 = from the bucket count)
+    bool table = false; // fixed-base window table (build_table() before the first run); dense scalars only
 };
 
 // Counters a finished MSM leaves behind (for bench.py's work model and tests)
@@ -546,6 +606,11 @@ public:
 
     // capacity for n points
     void reserve(size_t n, const MsmConfig& cfg_in = MsmConfig());
+
+    // cfg.table: build the window table of these bases (device pointer, n <= capacity) once; every later run must
+    // pass the same bases.  Returns the table's size in bytes.
+    size_t build_table(const aff* bases_, size_t n_, cudaStream_t s);
+    static size_t table_bytes(size_t n, int c) { return size_t(msm_num_windows(c)) * n * sizeof(aff); }
 
     // timeline of the last run relative to `base` (an event recorded earlier), milliseconds:
     // [0] start, [1] digits done, [2] sort + task counts done, [3] accumulate starts, [4] accumulate done, [5] window sums on the host
@@ -604,7 +669,8 @@ public:
     static void prepare() {}
 
     MsmStats stats;
-    int c = 0, W = 0;
+    int c = 0, W = 0;    // W = windows of the bucket problem (1 with a table)
+    int Wd = 0;          // digit windows = rows of the table
     uint32_t T = 0, L = 0, L1 = 4;
 
 private:
@@ -622,7 +688,13 @@ private:
         return v;
     }
     static constexpr int RED_THREADS = 128;
-    static constexpr uint32_t SUM_SLICES = 32;
+    // slices a window's chunk results are summed in before the one-CTA window sum: none below 1024 points, else about
+    // 4 points per thread of a 128-thread CTA, 32..256 slices
+    static uint32_t num_slices(uint32_t per_window) {
+        if (per_window < 1024) return 0;
+        uint32_t k = per_window / 512;
+        return k < 32 ? 32 : k > 256 ? 256 : k;
+    }
     static void grow(DevBuf& b, size_t bytes) {
         if (bytes > b.bytes) b.alloc(bytes + bytes / 4 + 4096);
     }
@@ -633,14 +705,15 @@ private:
     }
     MsmConfig cfg;
     size_t cap_n = 0, n = 0, m = 0, slots = 148 * 1024;
-    uint32_t bpw = 0, nb = 0, cpw = 0, cpw1 = 0;
+    uint32_t bpw = 0, nb = 0, cpw = 0, cpw1 = 0, ns0 = 0, ns1 = 0;
     const aff* bases = nullptr;
     cudaStream_t stream = 0;
     uint32_t *sorted_keys = nullptr, *sorted_vals = nullptr;
     DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
-        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, merged, prefix, chunk_out, chunk_sum, chunk2_out, slice_out,
+        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, merged, prefix, chunk_out, chunk_sum, chunk2_out, slice_out, slice1_out,
         window_out, counters, cub_tmp,
-        task_tmp;
+        task_tmp, table;
+    size_t table_n = 0;
     unsigned long long* h_counters = nullptr;
     pt* h_windows = nullptr;
     cudaEvent_t ev_mrg0 = nullptr, ev_mrg1 = nullptr;
@@ -655,14 +728,17 @@ template <class C>
 void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     cfg = cfg_in;
     cap_n = n;
-    c = cfg.c ? cfg.c : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
+    c = cfg.c ? cfg.c : cfg.table ? msm_pick_c_table(n) : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
     if (c < 2) c = 2;
     if (c > 24) c = 24;
-    W = msm_num_windows(c);
+    if (cfg.table && c < 6) c = 6;
+    Wd = msm_num_windows(c);
+    W = cfg.table ? 1 : Wd;
     bpw = 1u << (c - 1);
     nb = uint32_t(W) * bpw;
-    size_t m_max = n * size_t(W);
+    size_t m_max = n * size_t(Wd);
     if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
+    if (cfg.table && m_max > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM window table too large for 30-bit base indices; shard it");
     // level-0 chunks: 16 buckets when there are enough buckets to fill the machine with chunk threads, else 8
     // (half the dependency chain); level 1 works on bpw/L points only, so its chunks are short (latency, not work)
     L = cfg.L ? cfg.L : (nb >= (2u << 20) ? 16 : 8);
@@ -683,7 +759,10 @@ void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
     chunk_sum.alloc(size_t(W) * cpw * sizeof(pt));
     chunk2_out.alloc(size_t(W) * cpw1 * sizeof(pt));
-    slice_out.alloc(size_t(W) * SUM_SLICES * sizeof(pt));
+    ns0 = num_slices(cpw);
+    ns1 = num_slices(cpw1);
+    slice_out.alloc(size_t(W) * (ns0 ? ns0 : 1) * sizeof(pt));
+    slice1_out.alloc(size_t(W) * (ns1 ? ns1 : 1) * sizeof(pt));
     window_out.alloc(size_t(W) * sizeof(pt));
     counters.alloc(64);
     size_t t1 = 0, t3 = 0;
@@ -704,15 +783,29 @@ void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
 }
 
 template <class C>
+size_t Msm<C>::build_table(const aff* bases_, size_t n_, cudaStream_t s) {
+    if (!cfg.table) throw std::runtime_error("MSM: build_table without cfg.table");
+    if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
+    table_n = n_;
+    if (!n_) return 0;
+    table.alloc(size_t(Wd) * n_ * sizeof(aff));
+    msm_window_table_kernel<C><<<(unsigned)((n_ + 127) / 128), 128, 0, s>>>(bases_, (uint32_t)n_, c, Wd, table.template as<aff>());
+    G16_CUDA(cudaGetLastError());
+    return size_t(Wd) * n_ * sizeof(aff);
+}
+
+template <class C>
 void Msm<C>::stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
     if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
-    bases = bases_;
+    if (cfg.table && n_ != table_n) throw std::runtime_error("MSM: window table was built for a different base count");
+    bases = cfg.table && n_ ? table.template as<aff>() : bases_;
     n = n_;
     stream = s;
     G16_CUDA(cudaEventRecord(ev_t[0], s));
     G16_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
     if (n) {
-        msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, W,
+        msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd,
+                                                                      cfg.table ? (uint32_t)n : 0u,
                                                                       keys_a.as<uint32_t>(), vals_a.as<uint32_t>(),
                                                                       counters.as<unsigned long long>());
         G16_CUDA(cudaGetLastError());
@@ -737,7 +830,7 @@ void Msm<C>::stage2() {
     }
     if (T < T_MIN) T = T_MIN;
     stats = MsmStats();
-    stats.entries = m; stats.c = c; stats.W = W; stats.buckets = nb; stats.T = T;
+    stats.entries = m; stats.c = c; stats.W = Wd; stats.buckets = nb; stats.T = T;
     G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
     if (m == 0) {
         G16_CUDA(cudaEventRecord(ev_t[2], s));
@@ -857,17 +950,23 @@ void Msm<C>::stage3(cudaStream_t s3) {
         buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
     msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
         chunk_sum.as<pt>(), cpw, L1, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
-    const pt* a0 = chunk_out.as<pt>();
-    uint32_t n0 = cpw;
-    if (cpw >= 32 * SUM_SLICES) {  // long windows: sum the level-0 results in slices first (short dependency chains)
-        msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * SUM_SLICES, RED_THREADS, 0, s>>>(
-            chunk_out.as<pt>(), cpw, SUM_SLICES, slice_out.as<pt>());
+    // long windows: sum the level-0 and level-1 results in slices first, so that no thread of the one-CTA-per-window
+    // kernel below walks a long dependent chain of additions
+    const pt *a0 = chunk_out.as<pt>(), *a1 = chunk2_out.as<pt>();
+    uint32_t n0 = cpw, n1 = cpw1;
+    if (ns0) {
+        msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * ns0, RED_THREADS, 0, s>>>(chunk_out.as<pt>(), cpw, ns0, slice_out.as<pt>());
         a0 = slice_out.as<pt>();
-        n0 = SUM_SLICES;
+        n0 = ns0;
         G16_LAUNCHED(1);
     }
-    msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(a0, n0, chunk2_out.as<pt>(), cpw1, L,
-                                                                    window_out.as<pt>());
+    if (ns1) {
+        msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * ns1, RED_THREADS, 0, s>>>(chunk2_out.as<pt>(), cpw1, ns1, slice1_out.as<pt>());
+        a1 = slice1_out.as<pt>();
+        n1 = ns1;
+        G16_LAUNCHED(1);
+    }
+    msm_window_sum_kernel<C, RED_THREADS><<<W, RED_THREADS, 0, s>>>(a0, n0, a1, n1, L, window_out.as<pt>());
     G16_CUDA(cudaGetLastError());
     G16_LAUNCHED(3);
     G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));

@@ -227,7 +227,7 @@ static void set_device(int device) {
 
 template <class C>
 static void load_section(BaseSection<C>& sec, const Section& s, size_t rec, size_t expect, int rank, int count,
-                         int msm_c, bool sparse, cudaStream_t st, const char* name) {
+                         int msm_c, bool sparse, cudaStream_t st, const char* name, int table = 0) {
     if (s.size != expect * rec) throw FormatError(std::string("zkey: section ") + name + " has the wrong size");
     sec.lo = expect * size_t(rank) / size_t(count);
     size_t hi = expect * size_t(rank + 1) / size_t(count);
@@ -243,8 +243,22 @@ static void load_section(BaseSection<C>& sec, const Section& s, size_t rec, size
     MsmConfig cfg;
     cfg.c = msm_c;
     cfg.sparse = sparse;
+    if (table && sec.n) {
+        // fixed-base window table (msm_window_table_kernel): on when asked for, or when it fits in a quarter of the
+        // memory that is free right now
+        int c = msm_c ? (msm_c < 6 ? 6 : msm_c > 24 ? 24 : msm_c) : msm_pick_c_table(sec.n);
+        size_t need = Msm<C>::table_bytes(sec.n, c), free_b = 0, total_b = 0;
+        G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        bool fits = size_t(msm_num_windows(c)) * sec.n <= size_t(MSM_INDEX_MASK);
+        cfg.table = fits && (table > 1 || need <= free_b / 4);
+    }
     sec.msm.reserve(sec.n ? sec.n : 1, cfg);
+    if (cfg.table) sec.msm.build_table(sec.bases.template as<typename C::aff>(), sec.n, st);
 }
+
+#ifndef G16_H_TABLE_DEFAULT
+#define G16_H_TABLE_DEFAULT 1   // what opts.h_table == 0 means: 0 = off, 1 = on when it fits
+#endif
 
 static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opts) {
     g16_opts o;
@@ -310,7 +324,12 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     load_section<G2>(zk->B2, need(secs, 7, "zkey"), 128, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "7 (B2)");
     load_section<G1>(zk->C, need(secs, 8, "zkey"), 64, nv - zk->n_public - 1, zk->shard_rank, zk->shard_count, o.msm_c,
                      true, st, "8 (C)");
-    load_section<G1>(zk->H, need(secs, 9, "zkey"), 64, n, zk->shard_rank, zk->shard_count, o.msm_c, false, st, "9 (H)");
+    // H scalars are dense (every window of every scalar is live): the one section where a window table pays.
+    // opts.h_table / G16_H_TABLE: 1 = always, -1 = never, 0 = when it fits (see load_section)
+    int h_table = o.h_table;
+    if (const char* e = std::getenv("G16_H_TABLE")) h_table = std::atoi(e) > 0 ? 1 : -1;
+    load_section<G1>(zk->H, need(secs, 9, "zkey"), 64, n, zk->shard_rank, zk->shard_count, o.msm_c, false, st, "9 (H)",
+                     h_table > 0 ? 2 : h_table == 0 ? G16_H_TABLE_DEFAULT : 0);
 
     // section 4: coefficients -> CSR by (matrix, constraint)
     const Section& s4 = need(secs, 4, "zkey");
@@ -901,6 +920,7 @@ int g16_prove_files(const char* zkey_path, const char* wtns_path, const char* pr
         if (opts) o = *opts;
         else g16_opts_default(&o);
         o.shard_count = 1;
+        if (o.h_table == 0) o.h_table = -1;   // one proof per key: building the window table costs more than it saves
         // G16_VERBOSE: where the wall time of one command-line call goes (the reference's figure is GNU time around the
         // whole process, scripts/lib/cmd_executor.sh:6,17)
         const bool verbose = std::getenv("G16_VERBOSE") != nullptr;
