@@ -69,6 +69,7 @@ def main():
     ap.add_argument("--max-log", type=int, default=26)
     ap.add_argument("--max-log-g2", type=int, default=24)
     ap.add_argument("--iters", type=int, default=5)
+    ap.add_argument("--ntt-only", action="store_true", help="skip the MSM sweeps")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     import torch
@@ -84,7 +85,7 @@ def main():
         print(json.dumps(d), flush=True)
 
     imad_peak = pkg.bench_int_pipe(1)
-    for is_g2 in (False, True):
+    for is_g2 in (() if args.ntt_only else (False, True)):
         top = min(args.max_log, args.max_log_g2) if is_g2 else args.max_log
         if top < args.min_log:
             continue
