@@ -50,8 +50,16 @@ def run_pass(a, logn, s_lo, k, tw, dif, inverse, scale=None):
                     w = inter(lo, t)
                     if w is not None: v = v * w % R
                 sh[t * S + qi] = v
-        rs = range(k - 1, -1, -1) if dif else range(k)
-        for r in rs:
+        def bf(e0, e1, w, unit):
+            x, y = sh[e0], sh[e1]
+            if dif:
+                d = (x - y) % R
+                sh[e0] = (x + y) % R
+                sh[e1] = d if unit else d * w % R
+            else:
+                if not unit: y = y * w % R
+                sh[e0] = (x + y) % R; sh[e1] = (x - y) % R
+        def single(r):
             for u in range(tile // 2):
                 qi = u & (S - 1)
                 v = u >> logS
@@ -59,18 +67,36 @@ def run_pass(a, logn, s_lo, k, tw, dif, inverse, scale=None):
                 tl = v >> (k - 1 - r)
                 if qi >= Sq: continue
                 t0 = (th << (r + 1)) | tl
-                t1 = t0 + (1 << r)
-                e0, e1 = t0 * S + qi, t1 * S + qi
-                x, y = sh[e0], sh[e1]
-                unit = tl == 0
+                bf(t0 * S + qi, (t0 + (1 << r)) * S + qi, P[tl << (k - 1 - r)], tl == 0)
+        def pair(r):   # levels r and r+1 on 4 elements held by one thread
+            for gidx in range(tile // 4):
+                qi = gidx & (S - 1)
+                v = gidx >> logS
+                th = v & ((1 << (k - 2 - r)) - 1)
+                tl = v >> (k - 2 - r)
+                if qi >= Sq: continue
+                t00 = (th << (r + 2)) | tl
+                a = [(t00 + d) * S + qi for d in (0, 1 << r, 2 << r, 3 << r)]
                 w = P[tl << (k - 1 - r)]
+                w1 = P[tl << (k - 2 - r)]
+                w2 = P[(tl + (1 << r)) << (k - 2 - r)]
                 if dif:
-                    d = (x - y) % R
-                    sh[e0] = (x + y) % R
-                    sh[e1] = d if unit else d * w % R
+                    bf(a[0], a[2], w1, tl == 0); bf(a[1], a[3], w2, False)
+                    bf(a[0], a[1], w, tl == 0); bf(a[2], a[3], w, tl == 0)
                 else:
-                    if not unit: y = y * w % R
-                    sh[e0] = (x + y) % R; sh[e1] = (x - y) % R
+                    bf(a[0], a[1], w, tl == 0); bf(a[2], a[3], w, tl == 0)
+                    bf(a[0], a[2], w1, tl == 0); bf(a[1], a[3], w2, False)
+        if dif:
+            r = k - 1
+            if k & 1:
+                single(r); r -= 1
+            while r >= 1:
+                pair(r - 1); r -= 2
+        else:
+            r = 0
+            while r + 1 < k:
+                pair(r); r += 2
+            if k & 1: single(k - 1)
         for qi in range(Sq):
             q = q0 + qi
             hi, lo = q >> s_lo, q & ((1 << s_lo) - 1)
