@@ -71,6 +71,13 @@ int g16_witness_load(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len);
 int g16_prove_loaded(g16_zkey* zk, char* proof_json, size_t* proof_len, char* public_json, size_t* public_len,
                      const g16_opts* opts);
 
+/* Double-buffered witness for back-to-back proofs with one key (the batch loop of scripts/full_workflow.sh:503,534,552
+ * calls the prover once per batch with the same zkey): prefetch starts the host->device copy of the NEXT witness on its
+ * own stream and returns (asynchronous when `wtns` is page-locked; the caller keeps the buffer alive until commit);
+ * commit waits for that copy and makes it the witness g16_prove_loaded / g16_prove_partial use. */
+int g16_witness_prefetch(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len);
+int g16_witness_commit(g16_zkey* zk);
+
 /* the rapidsnark / snarkjs command line as one call: reads both files, writes both outputs */
 int g16_prove_files(const char* zkey_path, const char* wtns_path, const char* proof_path, const char* public_path,
                     const g16_opts* opts);

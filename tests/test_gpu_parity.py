@@ -443,6 +443,55 @@ def test_prove_closed_form_at_scale_with_h_window_table(pkg):
         assert a["additions"] < b["additions"] and a["c"] > b["c"]      # wider windows: fewer mixed additions
 
 
+def test_infinity_records_in_every_section(pkg, small_fixture):
+    """all-zero (infinity) records in sections 5-9, the zkey convention for wires a matrix never touches: skipped by the
+    digit kernels and by the H window table; the proof must equal the oracle's on the same edited key."""
+    import copy
+    f = small_fixture
+    zk = copy.deepcopy(f["zk"])
+    rng = random.Random(31)
+    for sec in (zk.A, zk.B1, zk.C, zk.H):
+        for i in rng.sample(range(len(sec)), max(1, len(sec) // 5)):
+            sec[i] = None
+    for i in rng.sample(range(len(zk.B2)), len(zk.B2) // 5):
+        zk.B2[i] = None
+        zk.B1[i] = None
+    zk.H[0] = None
+    zk.H[-1] = None
+    r, s = 77, 88
+    want = g16.prove(zk, f["w"], r, s)
+    raw = binfile.write_zkey(zk)
+    for h_table in (1, -1):
+        with pkg.ZKey(raw, h_table=h_table) as h:
+            assert h.prove(bytes(f["wtns_bytes"]), r=r, s=s) == want
+
+
+def test_prove_stream_double_buffered_witness(pkg, small_fixture):
+    """g16_witness_prefetch / g16_witness_commit: the next witness is copied while the current proof computes; each
+    proof must be the oracle's proof for ITS witness (also for a witness that does not satisfy the circuit: the prover,
+    like the reference's, does not check)."""
+    f = small_fixture
+    rng = random.Random(5)
+    w2 = list(f["w"])
+    for i in rng.sample(range(1, len(w2)), 20):
+        w2[i] = rng.randrange(R)
+    ws = [f["w"], w2, f["w"], w2, w2]
+    r, s = 31337, 271828
+    want = [g16.prove(f["zk"], w, r, s) for w in ws]
+    with pkg.ZKey(bytes(f["zkey_bytes"])) as zk:
+        got = list(zk.prove_stream([binfile.write_wtns(w) for w in ws], r=r, s=s))
+        assert got == want
+        assert want[0] != want[1]
+        assert list(zk.prove_stream([])) == []
+        with pytest.raises(pkg.G16Error):
+            zk.commit_witness()                       # nothing prefetched
+        with pytest.raises(pkg.G16Error) as e:
+            zk.prefetch_witness(binfile.write_wtns(f["w"][:-1]))
+        assert e.value.code == pkg.G16_ERR_WITNESS_LEN
+        # a failed prefetch leaves the loaded witness in place
+        assert zk.prove_loaded(r=r, s=s) == want[-1]
+
+
 SHARD_WORKER = r'''
 import os, sys, json
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))

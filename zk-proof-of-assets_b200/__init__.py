@@ -32,7 +32,7 @@ PARTIAL_BYTES = 768
 # every symbol include/g16_b200.h declares (tests check the built library exports all of them)
 ABI_SYMBOLS = [
     "g16_opts_default", "g16_last_error", "g16_version", "g16_zkey_open", "g16_zkey_open_mem", "g16_zkey_close",
-    "g16_zkey_info", "g16_prove", "g16_witness_load", "g16_prove_loaded", "g16_prove_files", "g16_prove_partial",
+    "g16_zkey_info", "g16_prove", "g16_witness_load", "g16_witness_prefetch", "g16_witness_commit", "g16_prove_loaded", "g16_prove_files", "g16_prove_partial",
     "g16_prove_combine", "g16_msm_g1_host", "g16_msm_g2_host", "g16_msm_create", "g16_msm_destroy", "g16_msm_run_dev",
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
@@ -90,6 +90,8 @@ def lib():
         L.g16_prove.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p,
                                 ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_witness_load.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+        L.g16_witness_prefetch.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+        L.g16_witness_commit.argtypes = [ctypes.c_void_p]
         L.g16_prove_loaded.argtypes = [ctypes.c_void_p] * 6
         L.g16_prove_files.argtypes = [ctypes.c_char_p] * 4 + [ctypes.c_void_p]
         L.g16_prove_partial.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
@@ -219,6 +221,34 @@ class ZKey:
 
     def load_witness(self, wtns):
         _check(lib().g16_witness_load(self._h, _addr(wtns), len(wtns)))
+
+    def prefetch_witness(self, wtns):
+        """start the host->device copy of the NEXT proof's witness (asynchronous when `wtns` is pinned host memory; keep
+        the buffer alive until commit_witness)"""
+        self._next_wtns = wtns
+        _check(lib().g16_witness_prefetch(self._h, _addr(wtns), len(wtns)))
+
+    def commit_witness(self):
+        """wait for the prefetched copy and make it the witness prove_loaded uses"""
+        _check(lib().g16_witness_commit(self._h))
+        self._next_wtns = None
+
+    def prove_stream(self, witnesses, r=None, s=None, style=STYLE_RAPIDSNARK):
+        """Back-to-back proofs with this key, the batch loop of scripts/full_workflow.sh:552 for one zkey: yields
+        (proof, public) per witness while the next witness is already being copied to the device."""
+        it = iter(witnesses)
+        try:
+            self.prefetch_witness(next(it))
+        except StopIteration:
+            return
+        more = True
+        while more:
+            self.commit_witness()
+            try:
+                self.prefetch_witness(next(it))
+            except StopIteration:
+                more = False
+            yield self.prove_loaded(r=r, s=s, style=style)
 
     def prove_loaded(self, r=None, s=None, style=STYLE_RAPIDSNARK):
         o = make_opts(style=style, r=r, s=s)

@@ -168,6 +168,11 @@ struct g16_zkey {
     BaseSection<G2> B2;
     DevBuf row_ptr, col, val;  // CSR of the A rows then the B rows (2n+1 pointers)
     DevBuf w;                  // witness, n_vars x 32 B standard form
+    DevBuf w_next;             // the witness of the NEXT proof, filled by g16_witness_prefetch while this one is proved
+    cudaStream_t s_copy = nullptr;
+    cudaEvent_t ev_copy = nullptr;
+    bool next_ready = false;
+    std::vector<uint8_t> next_public;
     DevBuf pa, pb, pc;         // A, B, C evaluations; pa ends up holding the H scalars
     NttDomain dom;
     cudaStream_t s_main = nullptr, s_msm[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -186,6 +191,8 @@ struct g16_zkey {
     ~g16_zkey() {
         cudaSetDevice(device);
         if (s_main) cudaStreamDestroy(s_main);
+        if (s_copy) cudaStreamDestroy(s_copy);
+        if (ev_copy) cudaEventDestroy(ev_copy);
         for (auto& s : s_pre)
             if (s) cudaStreamDestroy(s);
         for (auto& s : s_msm)
@@ -474,7 +481,8 @@ static std::string public_json(const std::vector<uint8_t>& pub, int style) {
 // ---------------------------------------------------------------------------------------------------------
 // witness (row a3)
 // ---------------------------------------------------------------------------------------------------------
-static void witness_load(g16_zkey* zk, const uint8_t* data, size_t len) {
+// header checks of a .wtns image; returns the payload (n_vars x 32 B, standard form)
+static const uint8_t* witness_check(const g16_zkey* zk, const uint8_t* data, size_t len) {
     auto secs = parse_binfile(data, len, "wtns", 2);
     const Section& s1 = need(secs, 1, "wtns");
     if (s1.size < 4) throw FormatError("wtns: header section too short");
@@ -488,6 +496,12 @@ static void witness_load(g16_zkey* zk, const uint8_t* data, size_t len) {
                                                    ", witness: " + std::to_string(nw));
     const Section& s2 = need(secs, 2, "wtns");
     if (s2.size != uint64_t(nw) * 32) throw FormatError("wtns: data section has the wrong size");
+    return s2.p;
+}
+
+static void witness_load(g16_zkey* zk, const uint8_t* data, size_t len) {
+    struct { const uint8_t* p; } s2{witness_check(zk, data, len)};
+    const uint32_t nw = zk->n_vars;
     G16_CUDA(cudaSetDevice(zk->device));
     G16_CUDA(cudaEventRecord(zk->ev[13], zk->s_main));
     G16_CUDA(cudaMemcpyAsync(zk->w.p, s2.p, size_t(nw) * 32, cudaMemcpyHostToDevice, zk->s_main));
@@ -814,6 +828,41 @@ int g16_witness_load(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len) {
     return guarded([&]() {
         if (!zk || !wtns) return fail(G16_ERR_GENERIC, "null argument");
         witness_load(zk, wtns, wtns_len);
+        return (int)G16_OK;
+    });
+}
+
+// Double-buffered witness: the host->device copy of the next proof's witness runs on its own stream while the current
+// proof computes; commit waits for it and swaps the buffers.
+int g16_witness_prefetch(g16_zkey* zk, const uint8_t* wtns, size_t wtns_len) {
+    return guarded([&]() {
+        if (!zk || !wtns) return fail(G16_ERR_GENERIC, "null argument");
+        const uint8_t* payload = witness_check(zk, wtns, wtns_len);
+        G16_CUDA(cudaSetDevice(zk->device));
+        if (!zk->s_copy) G16_CUDA(cudaStreamCreateWithFlags(&zk->s_copy, cudaStreamNonBlocking));
+        if (!zk->ev_copy) G16_CUDA(cudaEventCreateWithFlags(&zk->ev_copy, cudaEventDisableTiming));
+        if (!zk->w_next.p) zk->w_next.alloc(size_t(zk->n_vars) * 32);
+        G16_CUDA(cudaMemcpyAsync(zk->w_next.p, payload, size_t(zk->n_vars) * 32, cudaMemcpyHostToDevice, zk->s_copy));
+        G16_CUDA(cudaEventRecord(zk->ev_copy, zk->s_copy));
+        zk->next_public.assign(payload + 32, payload + 32 + size_t(zk->n_public) * 32);
+        zk->next_ready = true;
+        return (int)G16_OK;
+    });
+}
+
+int g16_witness_commit(g16_zkey* zk) {
+    return guarded([&]() {
+        if (!zk) return fail(G16_ERR_GENERIC, "null handle");
+        if (!zk->next_ready) return fail(G16_ERR_GENERIC, "no prefetched witness: call g16_witness_prefetch first");
+        G16_CUDA(cudaSetDevice(zk->device));
+        G16_CUDA(cudaEventSynchronize(zk->ev_copy));
+        std::swap(zk->w.p, zk->w_next.p);
+        std::swap(zk->w.bytes, zk->w_next.bytes);
+        zk->public_bytes.swap(zk->next_public);
+        zk->next_ready = false;
+        zk->t_ms[0] = 0;
+        zk->witness_loaded = true;
+        zk->partial_done = false;
         return (int)G16_OK;
     });
 }
