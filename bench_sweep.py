@@ -70,6 +70,7 @@ def main():
     ap.add_argument("--max-log-g2", type=int, default=24)
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--ntt-only", action="store_true", help="skip the MSM sweeps")
+    ap.add_argument("--apply-key", action="store_true", help="with --ntt-only: still time the batch apply-key operator")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     import torch
@@ -157,6 +158,37 @@ def main():
               "frac_of_hbm_peak_strict": (3 * 128 * n / med / 1e9 / hbm) if hbm else None,
               "modmul_per_s": modmuls / med, "frac_of_modmul_peak": modmuls / med / modmul_peak})
         del a
+    # batch apply key (operator level): out[i] = (first * inc^i) * P_i on device-resident records
+    if not args.ntt_only or args.apply_key:
+        for is_g2, lg in ((False, min(args.max_log, 21)), (True, min(args.max_log, 19))):
+            n = 1 << lg
+            rec = 128 if is_g2 else 64
+            kb = np.zeros((n, 4), dtype=np.uint64)
+            kb[:, 0] = rng.integers(1, 1 << 31, size=n, dtype=np.uint64)
+            pts = pkg.fixed_base(is_g2, kb.tobytes(), n)
+            d_p = torch.frombuffer(bytearray(pts), dtype=torch.uint8).to(dev)
+            d_o = torch.empty_like(d_p)
+            first = int(rng.integers(1, 1 << 62)) << 190 | 12345
+            ts = []
+            for it in range(1 + 3):
+                torch.cuda.synchronize(dev)
+                t = time.perf_counter()
+                pkg.batch_apply_key_dev(is_g2, d_p.data_ptr(), n, first, 1, d_o.data_ptr())
+                dt = time.perf_counter() - t
+                if it >= 1:
+                    ts.append(dt)
+            med = statistics.median(ts)
+            # spot check against the fixed-base generator: (first * k_0) * G
+            want = pkg.fixed_base(is_g2, (first * int(kb[0, 0]) % R).to_bytes(32, "little"), 1)
+            ok = bytes(d_o[:rec].cpu().numpy().tobytes()) == want
+            popcnt = bin(first % R).count("1")
+            mm = (254 * 9 + popcnt * 10 + 400) * (3 if is_g2 else 1)
+            emit({"op": "apply_key_g2" if is_g2 else "apply_key_g1", "log_n": lg, "n": n, "ms": med * 1e3,
+                  "mpts_per_s": n / med / 1e6, "modmul_per_point_model": mm, "modmul_per_s": mm * n / med,
+                  "frac_of_modmul_peak": mm * n / med / modmul_peak, "correct": bool(ok)})
+            if not ok:
+                raise SystemExit("apply key result differs from the closed form")
+            del d_p, d_o
     print("\nop | log n | scalars | ms | Mpts/s | frac of int peak", file=sys.stderr)
     for d in lines:
         print("%s | %d | %s | %.3f | %.1f | %.2f" % (d["op"], d["log_n"], d.get("scalars", "-"), d["ms"], d["mpts_per_s"],

@@ -134,6 +134,18 @@ int g16_msm_stats(const g16_msm* m, uint64_t out[6]);
 int g16_h_scalars(g16_zkey* zk, uint8_t* out);
 /* same pipeline, result left on the device (measurement helper: no device->host copy in the call) */
 int g16_h_pipeline_dev(g16_zkey* zk);
+
+/* out[i] = (first * inc^i) * P_i, i < n -- ffjavascript 0.2.62 engine_applykey.js `G.batchApplyKey(buff, first, inc)`:
+ * the kernel of `snarkjs zkey contribute` / `zkey beacon` (sections 8 and 9 times 1/delta'; reference call site
+ * scripts/g16_setup.sh:240-283) and of the powers-of-tau steps.  SURVEY.md 8(f) rank 2 at operator level: the
+ * ceremony bookkeeping (transcript hashes, section 10) stays with snarkjs.  points/out: n records in the zkey layout
+ * (64 B G1 / 128 B G2, affine, Montgomery, all-zero = infinity); first, inc: 32 B little-endian, standard form, < r.
+ * The _dev form takes device pointers (out may equal points). */
+int g16_batch_apply_key(int is_g2, const uint8_t* points, size_t n, const uint8_t first[32], const uint8_t inc[32],
+                        uint8_t* out, const g16_opts* opts);
+int g16_batch_apply_key_dev(int is_g2, const void* d_points, size_t n, const uint8_t first[32], const uint8_t inc[32],
+                            void* d_out);
+
 /* odd-coset transform of `count` device-resident vectors of 2^logn Montgomery Fr elements, in place:
  * iNTT, multiply by inc^i, NTT (rows a5-a7).  d_data: count x 2^logn x 32 B. */
 int g16_coset_ntt_dev(void* d_data, int logn, int count);

@@ -492,6 +492,55 @@ def test_prove_stream_double_buffered_witness(pkg, small_fixture):
         assert zk.prove_loaded(r=r, s=s) == want[-1]
 
 
+# ---- batch apply key (operator level) ---------------------------------------------------
+@pytest.mark.parametrize("is_g2", [False, True])
+def test_batch_apply_key_matches_oracle_scalar_multiplication(pkg, is_g2):
+    """out[i] = (first * inc^i) * P_i, ffjavascript G.batchApplyKey; inc = 1 is the `zkey contribute` case (every point of
+    sections 8 and 9 times 1/delta').  Oracle: double-and-add in Python."""
+    rng = random.Random(2024 + is_g2)
+    G, gen, rec, dec = (bn.G2, bn.G2_GEN, rec_g2, binfile.dec_g2) if is_g2 else (bn.G1, bn.G1_GEN, rec_g1, binfile.dec_g1)
+    size = 128 if is_g2 else 64
+    n = 12 if is_g2 else 40
+    pts = [G.mul(gen, rng.randrange(1, R)) for _ in range(n)]
+    pts[3] = None                                   # infinity record stays infinity
+    raw = b"".join(rec(p) for p in pts)
+    for first, inc in ((rng.randrange(1, R), 1), (rng.randrange(1, R), rng.randrange(2, R)), (1, 1), (R - 1, 1), (0, 5), (7, 0)):
+        out = pkg.batch_apply_key(is_g2, raw, n, first, inc)
+        for i, p in enumerate(pts):
+            k = first * pow(inc, i, R) % R
+            want = None if p is None or k == 0 else G.mul(p, k)
+            assert dec(out[size * i:size * i + size]) == want, (first, inc, i)
+    assert pkg.batch_apply_key(is_g2, b"", 0, 5, 1) == b""
+    with pytest.raises(pkg.G16Error):
+        pkg.batch_apply_key(is_g2, raw, n, R, 1)     # scalar not reduced
+
+
+def test_batch_apply_key_is_the_contribute_update_of_sections_8_and_9(pkg, small_fixture):
+    """A `zkey contribute` with secret d turns delta into d*delta and sections 8 (C) and 9 (H) into (1/d) times
+    themselves (snarkjs zkey_contribute.js); a key updated that way with this operator must still produce proofs
+    that verify against the vkey with the updated delta."""
+    import copy
+    f = small_fixture
+    d = 0x1234567890ABCDEF1234567
+    dinv = pow(d, -1, R)
+    zk = copy.deepcopy(f["zk"])
+    c_raw = b"".join(rec_g1(p) for p in zk.C)
+    h_raw = b"".join(rec_g1(p) for p in zk.H)
+    c_new = pkg.batch_apply_key(False, c_raw, len(zk.C), dinv, 1)
+    h_new = pkg.batch_apply_key(False, h_raw, len(zk.H), dinv, 1)
+    zk.C = [binfile.dec_g1(c_new[64 * i:64 * i + 64]) for i in range(len(zk.C))]
+    zk.H = [binfile.dec_g1(h_new[64 * i:64 * i + 64]) for i in range(len(zk.H))]
+    zk.delta1 = bn.G1.mul(zk.delta1, d)
+    zk.delta2 = bn.G2.mul(zk.delta2, d)
+    vkey = copy.deepcopy(f["vkey"])
+    x, y = zk.delta2
+    vkey["vk_delta_2"] = [[str(x[0]), str(x[1])], [str(y[0]), str(y[1])], ["1", "0"]]
+    with pkg.ZKey(binfile.write_zkey(zk)) as h:
+        proof, public = h.prove(bytes(f["wtns_bytes"]))
+    assert V.verify(vkey, json.loads(public), json.loads(proof))
+    assert not V.verify(f["vkey"], json.loads(public), json.loads(proof))     # the old delta no longer fits
+
+
 SHARD_WORKER = r'''
 import os, sys, json
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))

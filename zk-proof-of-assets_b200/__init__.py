@@ -32,7 +32,7 @@ PARTIAL_BYTES = 768
 # every symbol include/g16_b200.h declares (tests check the built library exports all of them)
 ABI_SYMBOLS = [
     "g16_opts_default", "g16_last_error", "g16_version", "g16_zkey_open", "g16_zkey_open_mem", "g16_zkey_close",
-    "g16_zkey_info", "g16_prove", "g16_witness_load", "g16_witness_prefetch", "g16_witness_commit", "g16_prove_loaded", "g16_prove_files", "g16_prove_partial",
+    "g16_batch_apply_key", "g16_batch_apply_key_dev", "g16_zkey_info", "g16_prove", "g16_witness_load", "g16_witness_prefetch", "g16_witness_commit", "g16_prove_loaded", "g16_prove_files", "g16_prove_partial",
     "g16_prove_combine", "g16_msm_g1_host", "g16_msm_g2_host", "g16_msm_create", "g16_msm_destroy", "g16_msm_run_dev",
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
@@ -99,6 +99,10 @@ def lib():
         L.g16_h_scalars.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         L.g16_h_pipeline_dev.argtypes = [ctypes.c_void_p]
         L.g16_coset_ntt_dev.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        L.g16_batch_apply_key.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_char_p,
+                                          ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_batch_apply_key_dev.argtypes = [ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p,
+                                              ctypes.c_char_p, ctypes.c_void_p]
         L.g16_coset_ntt_host.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.g16_test_field_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_size_t]
         L.g16_test_curve_op.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
@@ -416,6 +420,22 @@ def coset_ntt_host(data, logn):
     buf = ctypes.create_string_buffer(bytes(data), len(data))
     _check(lib().g16_coset_ntt_host(buf, logn))
     return buf.raw
+
+
+def batch_apply_key(is_g2, points, n, first, inc=1, device=-1):
+    """out[i] = (first * inc^i) * P_i over n zkey-layout records in host memory -- ffjavascript `G.batchApplyKey`, the kernel
+    of `snarkjs zkey contribute` / `beacon` (operator level).  first, inc: ints below r."""
+    out = ctypes.create_string_buffer((128 if is_g2 else 64) * n)
+    o = make_opts(device=device)
+    _check(lib().g16_batch_apply_key(int(is_g2), _addr(points), n, int(first).to_bytes(32, "little"),
+                                     int(inc).to_bytes(32, "little"), out, ctypes.byref(o)))
+    return out.raw
+
+
+def batch_apply_key_dev(is_g2, d_points, n, first, inc=1, d_out=None):
+    """the same over device-resident records (in place unless d_out is given)"""
+    _check(lib().g16_batch_apply_key_dev(int(is_g2), d_points, n, int(first).to_bytes(32, "little"),
+                                         int(inc).to_bytes(32, "little"), d_points if d_out is None else d_out))
 
 
 def coset_ntt_dev(d_ptr, logn, count=1):

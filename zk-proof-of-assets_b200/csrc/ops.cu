@@ -152,6 +152,85 @@ int curve_op(int op, const uint8_t* points, size_t n, uint8_t* out, void (*conv)
     return G16_OK;
 }
 
+// ---- batch apply key (operator level) ---------------------------------------------------
+// out[i] = (first * inc^i) * P_i -- ffjavascript 0.2.62 engine_applykey.js `G.batchApplyKey(buff, first, inc)`, the
+// kernel of `snarkjs zkey contribute` / `zkey beacon` (sections 8 and 9 times 1/delta', scripts/g16_setup.sh:240-283)
+// and of the powers-of-tau steps.  One thread per point: its scalar from the binary powers of inc (the table trick of
+// ntt_powers_kernel), 254 doublings + a mixed addition per set bit in XYZZ, one Fermat inversion back to affine.
+template <class C>
+__global__ void __launch_bounds__(128)
+apply_key_kernel(const typename C::aff* __restrict__ pts, size_t n, fe_t first_m, const fe_t* __restrict__ pw, int bits,
+                 typename C::aff* __restrict__ out) {
+    typedef typename C::field F;
+    typedef typename C::fe fe;
+    typedef typename C::aff aff;
+    typedef typename C::pt pt;
+    size_t i = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
+    if (i >= n) return;
+    aff q = pts[i];
+    if (C::is_inf(q)) {
+        out[i] = q;
+        return;
+    }
+    fe_t k = first_m;
+    for (int b = 0; b < bits; b++)
+        if ((i >> b) & 1) k = Fr::mul(k, pw[b]);
+    k = Fr::from_mont(k);
+    pt acc = C::identity();
+    for (int bit = 253; bit >= 0; bit--) {
+        acc = C::dbl(acc);
+        if ((k.v[bit >> 5] >> (bit & 31)) & 1) C::madd(acc, q);
+    }
+    aff r;
+    if (C::is_identity(acc)) {
+        r.x = F::zero();
+        r.y = F::zero();
+    } else {
+        fe u = F::inv(acc.zzz);           // 1 / Z^3
+        fe zi = F::mul(u, acc.zz);        // 1 / Z
+        r.x = F::mul(acc.x, F::sqr(zi));
+        r.y = F::mul(acc.y, u);
+    }
+    out[i] = r;
+}
+
+static bool scalar_from_bytes(const uint8_t* b, U256& out) {
+    out = u256_from_bytes(b);
+    U256 m = HFr::mod();
+    for (int i = 3; i >= 0; i--) {
+        if (out.v[i] != m.v[i]) return out.v[i] < m.v[i];
+    }
+    return false;  // == r
+}
+
+static int apply_key_dev(int is_g2, const void* d_points, size_t n, const uint8_t* first, const uint8_t* inc, void* d_out,
+                         cudaStream_t s) {
+    U256 f, c;
+    if (!scalar_from_bytes(first, f) || !scalar_from_bytes(inc, c)) return fail(G16_ERR_GENERIC, "apply key: scalar not below r");
+    if (!n) return (int)G16_OK;
+    fe_t pw[64], first_m;
+    U256 fm = HFr::to_mont(f), a = HFr::to_mont(c);
+    std::memcpy(&first_m, fm.v, 32);
+    int bits = 0;
+    while (bits < 64 && (n - 1) >> bits) bits++;
+    for (int b = 0; b < 64; b++) {
+        std::memcpy(&pw[b], a.v, 32);
+        a = HFr::sqr(a);
+    }
+    DevBuf dpw;
+    dpw.alloc(sizeof(pw));
+    G16_CUDA(cudaMemcpyAsync(dpw.p, pw, sizeof(pw), cudaMemcpyHostToDevice, s));
+    unsigned grid = (unsigned)((n + 127) / 128);
+    if (is_g2)
+        apply_key_kernel<G2><<<grid, 128, 0, s>>>((const G2::aff*)d_points, n, first_m, dpw.as<fe_t>(), bits, (G2::aff*)d_out);
+    else
+        apply_key_kernel<G1><<<grid, 128, 0, s>>>((const G1::aff*)d_points, n, first_m, dpw.as<fe_t>(), bits, (G1::aff*)d_out);
+    G16_CUDA(cudaGetLastError());
+    G16_LAUNCHED(1);
+    G16_CUDA(cudaStreamSynchronize(s));
+    return (int)G16_OK;
+}
+
 // ---- integer-pipe microbenchmark ------------------------------------------------------------------------------
 // 8 independent accumulators per thread, long unrolled loops; results folded into one store so nothing is elided.
 __global__ void int_pipe_kernel(int op, int iters, uint32_t seed, uint32_t* out) {
@@ -337,6 +416,32 @@ int g16_coset_ntt_host(uint8_t* data, int logn) {
         dom.init(logn, 0);
         dom.to_odd_coset(d.as<fe_t>(), 0);
         G16_CUDA(cudaMemcpy(data, d.p, bytes, cudaMemcpyDeviceToHost));
+        return (int)G16_OK;
+    });
+}
+
+int g16_batch_apply_key_dev(int is_g2, const void* d_points, size_t n, const uint8_t first[32], const uint8_t inc[32],
+                            void* d_out) {
+    return guarded([&]() {
+        if ((!d_points || !d_out) && n) return fail(G16_ERR_GENERIC, "null argument");
+        if (!first || !inc) return fail(G16_ERR_GENERIC, "null argument");
+        return apply_key_dev(is_g2, d_points, n, first, inc, d_out, 0);
+    });
+}
+
+int g16_batch_apply_key(int is_g2, const uint8_t* points, size_t n, const uint8_t first[32], const uint8_t inc[32],
+                        uint8_t* out, const g16_opts* opts) {
+    return guarded([&]() {
+        if ((!points || !out) && n) return fail(G16_ERR_GENERIC, "null argument");
+        if (!first || !inc) return fail(G16_ERR_GENERIC, "null argument");
+        use_device(opts);
+        size_t rec = is_g2 ? 128 : 64;
+        DevBuf d;
+        d.alloc(n * rec);
+        G16_CUDA(cudaMemcpy(d.p, points, n * rec, cudaMemcpyHostToDevice));
+        int rc = apply_key_dev(is_g2, d.p, n, first, inc, d.p, 0);   // in place: a thread reads its record before it writes it
+        if (rc != G16_OK) return rc;
+        G16_CUDA(cudaMemcpy(out, d.p, n * rec, cudaMemcpyDeviceToHost));
         return (int)G16_OK;
     });
 }
