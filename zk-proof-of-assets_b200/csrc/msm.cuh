@@ -515,6 +515,44 @@ msm_sum_slices_kernel(const typename C::pt* __restrict__ in, uint32_t per_window
     if (threadIdx.x == 0) out[blockIdx.x] = acc;
 }
 
+// Level 1 of the bucket reduction and the slice sums of the level-0 results in ONE launch (both read only level-0
+// output, both are latency-bound on few threads, so they overlap instead of queueing): CTAs [0, W * slices) sum
+// slices of a0, the rest run the level-1 chunks (zero-based weights, chunk offset by double-and-add).
+template <class C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+msm_level1_kernel(const typename C::pt* __restrict__ a0, uint32_t per_window, uint32_t slices, uint32_t slice_ctas,
+                  typename C::pt* __restrict__ slice_out, const typename C::pt* __restrict__ s0, uint32_t L1,
+                  uint32_t chunks_per_window, uint32_t nchunks, typename C::pt* __restrict__ a1_out) {
+    typedef typename C::pt pt;
+    if (blockIdx.x < slice_ctas) {
+        uint32_t w = blockIdx.x / slices, p = blockIdx.x % slices;
+        uint32_t len = (per_window + slices - 1) / slices;
+        uint32_t lo = p * len, hi = min(lo + len, per_window);
+        const pt* X = a0 + size_t(w) * per_window;
+        pt acc = C::identity();
+        for (uint32_t i = lo + threadIdx.x; i < hi; i += THREADS) C::add(acc, X[i]);
+        block_sum_points<C, THREADS>(acc);
+        if (threadIdx.x == 0) slice_out[blockIdx.x] = acc;
+        return;
+    }
+    uint32_t t = (blockIdx.x - slice_ctas) * THREADS + threadIdx.x;
+    if (t >= nchunks) return;
+    uint32_t w = t / chunks_per_window, ch = t % chunks_per_window;
+    uint32_t lo = ch * L1;
+    uint32_t hi = min(lo + L1, per_window);
+    const pt* X = s0 + size_t(w) * per_window;
+    pt run = C::identity(), acc = C::identity();
+    for (uint32_t b = hi; b-- > lo;) {
+        C::add(acc, run);
+        C::add(run, X[b]);
+    }
+    if (lo) {
+        pt s = C::mul_small(run, lo);
+        C::add(acc, s);
+    }
+    a1_out[t] = acc;
+}
+
 // one CTA per window: window sum = sum of a0[n0] + L * sum of a1[n1]
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
@@ -525,14 +563,13 @@ msm_window_sum_kernel(const typename C::pt* __restrict__ a0, uint32_t n0, const 
     typename C::pt acc = C::identity(), hi = C::identity();
     for (uint32_t i = threadIdx.x; i < n0; i += THREADS) C::add(acc, p[i]);
     for (uint32_t i = threadIdx.x; i < n1; i += THREADS) C::add(hi, q[i]);
-    block_sum_points<C, THREADS>(acc);
-    __syncthreads();
-    block_sum_points<C, THREADS>(hi);
-    if (threadIdx.x == 0) {
-        typename C::pt s = C::mul_small(hi, L);
-        C::add(acc, s);
-        window_out[blockIdx.x] = acc;
+    // L * (sum of hi) = sum of L * hi: the weight is applied per thread so that ONE block tree finishes the window
+    if (!C::is_identity(hi)) {
+        hi = C::mul_small(hi, L);
+        C::add(acc, hi);
     }
+    block_sum_points<C, THREADS>(acc);
+    if (threadIdx.x == 0) window_out[blockIdx.x] = acc;
 }
 
 #endif  // G16_MSM_INSTANTIATE
@@ -948,17 +985,20 @@ void Msm<C>::stage3(cudaStream_t s3) {
     uint32_t nchunks = uint32_t(W) * cpw, nchunks1 = uint32_t(W) * cpw1;
     msm_chunk_reduce_kernel<C, true, false><<<(nchunks + 63) / 64, 64, 0, s>>>(
         buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
-    msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
-        chunk_sum.as<pt>(), cpw, L1, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
-    // long windows: sum the level-0 and level-1 results in slices first, so that no thread of the one-CTA-per-window
-    // kernel below walks a long dependent chain of additions
     const pt *a0 = chunk_out.as<pt>(), *a1 = chunk2_out.as<pt>();
     uint32_t n0 = cpw, n1 = cpw1;
     if (ns0) {
-        msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * ns0, RED_THREADS, 0, s>>>(chunk_out.as<pt>(), cpw, ns0, slice_out.as<pt>());
+        // long windows: level 1 and the slice sums of the level-0 results share a launch (msm_level1_kernel); slices
+        // keep every thread of the one-CTA-per-window sum below off a long dependent chain of additions
+        uint32_t slice_ctas = uint32_t(W) * ns0;
+        msm_level1_kernel<C, RED_THREADS><<<slice_ctas + (nchunks1 + RED_THREADS - 1) / RED_THREADS, RED_THREADS, 0, s>>>(
+            chunk_out.as<pt>(), cpw, ns0, slice_ctas, slice_out.as<pt>(), chunk_sum.as<pt>(), L1, cpw1, nchunks1,
+            chunk2_out.as<pt>());
         a0 = slice_out.as<pt>();
         n0 = ns0;
-        G16_LAUNCHED(1);
+    } else {
+        msm_chunk_reduce_kernel<C, false, true><<<(nchunks1 + 63) / 64, 64, 0, s>>>(
+            chunk_sum.as<pt>(), cpw, L1, cpw1, nchunks1, chunk2_out.as<pt>(), nullptr);
     }
     if (ns1) {
         msm_sum_slices_kernel<C, RED_THREADS><<<uint32_t(W) * ns1, RED_THREADS, 0, s>>>(chunk2_out.as<pt>(), cpw1, ns1, slice1_out.as<pt>());
