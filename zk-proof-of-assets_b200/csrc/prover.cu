@@ -272,6 +272,9 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     if (opts) o = *opts;
     else g16_opts_default(&o);
     set_device(o.device);
+    // G16_L2_FETCH=<32|64|128>: the device's L2 fetch granularity hint (experiment: the H accumulation reads 64-byte
+    // rows scattered over a table far larger than L2)
+    if (const char* e = std::getenv("G16_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
     std::unique_ptr<g16_zkey> zk(new g16_zkey());
     G16_CUDA(cudaGetDevice(&zk->device));
     zk->shard_count = o.shard_count > 1 ? o.shard_count : 1;
