@@ -73,3 +73,38 @@ def test_partial_gather_gloo_world2(tmp_path):
     for rank, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, o
         assert "rank %d ok" % rank in o
+
+
+def test_prove_stream_orders_prefetch_commit_and_prove():
+    """host logic of ZKey.prove_stream (no GPU): witness i+1 is handed to the copy stream BEFORE proof i is computed,
+    every witness is committed exactly once, nothing is prefetched after the last one"""
+    from conftest import load_pkg
+    pkg = load_pkg()
+    log = []
+
+    class Fake(pkg.ZKey):
+        def __init__(self):
+            pass
+
+        def __del__(self):
+            pass
+
+        def prefetch_witness(self, w):
+            log.append(("prefetch", w))
+
+        def commit_witness(self):
+            log.append(("commit",))
+
+        def prove_loaded(self, r=None, s=None, style=0):
+            log.append(("prove",))
+            return ("proof%d" % sum(1 for x in log if x[0] == "prove"), "public")
+
+    out = list(Fake().prove_stream(["w0", "w1", "w2"]))
+    assert [p for p, _ in out] == ["proof1", "proof2", "proof3"]
+    assert log == [("prefetch", "w0"), ("commit",), ("prefetch", "w1"), ("prove",), ("commit",), ("prefetch", "w2"),
+                   ("prove",), ("commit",), ("prove",)]
+    log.clear()
+    assert list(Fake().prove_stream([])) == [] and log == []
+    log.clear()
+    assert len(list(Fake().prove_stream(iter(["only"])))) == 1
+    assert log == [("prefetch", "only"), ("commit",), ("prove",)]
