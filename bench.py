@@ -7,14 +7,19 @@
 A "step" is one Groth16 prove (the thing scripts/g16_prove.sh:246-260 of the reference execs a prover for) of one
 witness against a resident proving key.  Metric = constraints proven per second (BASELINE.json: "Groth16 prove s &
 constraints/s per layer"); `ms_per_step` is the prove time, `msm_mpts_per_s` the MSM point rate inside it.
-  value : witness already in HBM (g16_witness_load done), timed g16_prove_loaded, CUDA-side work + host finalisation
-  e2e   : the public call ZKey.prove(wtns bytes in pinned host memory) -> JSON texts in host memory, per step
-N > 1   : one process per GPU, every rank proves its own independent batch proof (the reference's GNU-parallel batch
-          loop, scripts/full_workflow.sh:552): weak scaling, no data-path collective; barrier + max over ranks.
-          --mode shard: ONE proof over all ranks instead (strong scaling; NCCL for slices and 768-byte partials).
+  value      : witness already in HBM (g16_witness_load done), timed g16_prove_loaded, CUDA-side work + host finalisation
+  e2e        : the public call ZKey.prove(wtns bytes in pinned host memory) -> JSON texts in host memory, per step
+  per_config : N = 1 only; the larger BASELINE configurations (l1-16sigs 2^24, c1-layer-three 2^25) measured the same
+               way in the same run with fewer steps (--per-config none to skip)
+N > 1        : one process per GPU, every rank proves its own independent batch proof (the reference's GNU-parallel
+               batch loop, scripts/full_workflow.sh:552): weak scaling, no data-path collective; barrier + max over
+               ranks.  The same run then measures ONE proof over all ranks (base-range shards, NCCL for slices and
+               768-byte partials) and reports it under "strong".  --mode shard|shard-rep makes that the headline instead.
 Inputs are synthetic (SYNTH-1 circuits shaped like the reference's layers, known-trapdoor setup): the reference commits
 no .zkey/.wtns and none can be generated offline.  The reference arm (--impl reference) times the CPU oracle port
-(oracle/c/oracle.c, all host threads) because neither rapidsnark nor snarkjs can be installed here.
+(oracle/c/oracle.c, all host threads) on the SAME workload, because neither rapidsnark nor snarkjs can be installed
+here; it makes its fixture on the host cores too (oracle/c/synth1.h), so that arm loads none of the repository's CUDA
+libraries and never touches the GPU.
 """
 import argparse
 import importlib.util
@@ -39,8 +44,11 @@ WORKLOADS = {
     "tiny": (30000, 1, 32000, "smoke-sized circuit, domain 2^15"),
 }
 DEFAULT_WORKLOAD = "c2-layer-one"
+DEFAULT_PER_CONFIG = "l1-16sigs,c1-layer-three"
 CIRCUIT_SEED, TRAPDOOR_SEED = 0xB2000001, 0xB2000002
 CACHE_DIR = os.environ.get("G16_BENCH_CACHE", "/tmp/g16_bench_cache")
+# pinned blinding factors: the bit-exact self-check of every run, and the sharded modes (all ranks must agree)
+R_PIN, S_PIN = 0x1234567 << 200, 0x7654321 << 190
 
 
 def load_pkg():
@@ -53,13 +61,28 @@ def load_pkg():
     return mod
 
 
-def fixture(name, rank=0):
-    """(zkey bytes, wtns bytes) of a workload; generated once per box (GPU fixed-base multiplications through
-    libg16synth.so, which is bench support and not part of either timed arm) and cached under CACHE_DIR."""
+def proof_object(pts):
+    """closed-form (pi_a, pi_b, pi_c) affine ints -> the dict a rapidsnark-style proof.json parses to"""
+    a, b, c = pts
+    return {"pi_a": [str(a[0]), str(a[1]), "1"],
+            "pi_b": [[str(b[0][0]), str(b[0][1])], [str(b[1][0]), str(b[1][1])], ["1", "0"]],
+            "pi_c": [str(c[0]), str(c[1]), "1"], "protocol": "groth16"}
+
+
+def fixture_paths(name):
+    base = os.path.join(CACHE_DIR, name)
+    return base + ".zkey", base + ".wtns", base + ".vkey.json", base + ".expected.json"
+
+
+def fixture(name, maker="gpu", load=True):
+    """(zkey bytes, wtns bytes) of a workload, generated once per box and cached under CACHE_DIR together with its
+    verification key and the closed-form proof for (R_PIN, S_PIN).  maker = "gpu": fixed-base multiplications through
+    libg16synth.so (bench support, not part of either timed arm); "cpu": oracle/c/synth1.h on the host cores (what the
+    reference arm uses: no repository CUDA library, no GPU).  Both write the same bytes."""
     nv, npub, ncons, _ = WORKLOADS[name]
     os.makedirs(CACHE_DIR, exist_ok=True)
-    zp, wp = os.path.join(CACHE_DIR, name + ".zkey"), os.path.join(CACHE_DIR, name + ".wtns")
-    if not (os.path.exists(zp) and os.path.exists(wp)):
+    zp, wp, vp, ep = fixture_paths(name)
+    if not all(os.path.exists(p) for p in (zp, wp, vp, ep)):
         lock = zp + ".lock"
         try:
             fd = os.open(lock, os.O_CREAT | os.O_EXCL | os.O_WRONLY)
@@ -67,12 +90,18 @@ def fixture(name, rank=0):
             fd = None
         if fd is not None:
             try:
-                pkg = load_pkg()
-                sy = pkg.Synth(nv, npub, ncons, CIRCUIT_SEED, TRAPDOOR_SEED)
+                if maker == "cpu":
+                    from oracle import cport
+                    sy = cport.Synth(nv, npub, ncons, CIRCUIT_SEED, TRAPDOOR_SEED)
+                else:
+                    sy = load_pkg().Synth(nv, npub, ncons, CIRCUIT_SEED, TRAPDOOR_SEED)
                 zk, wt = sy.write()
                 vk = json.dumps(sy.vkey()).encode()
-                sy.close()
-                for path, data in ((zp[:-5] + ".vkey.json", vk), (wp, wt), (zp, zk)):
+                ex = json.dumps({"r": str(R_PIN), "s": str(S_PIN), "maker": maker,
+                                 "proof": proof_object(sy.expected(R_PIN, S_PIN))}).encode()
+                if hasattr(sy, "close"):
+                    sy.close()
+                for path, data in ((vp, vk), (ep, ex), (wp, wt), (zp, zk)):
                     with open(path + ".tmp", "wb") as f:
                         f.write(data)
                     os.replace(path + ".tmp", path)
@@ -82,11 +111,18 @@ def fixture(name, rank=0):
         else:
             while os.path.exists(lock):
                 time.sleep(0.5)
+    if not load:
+        return None, None
     with open(zp, "rb") as f:
         zk = f.read()
     with open(wp, "rb") as f:
         wt = f.read()
     return zk, wt
+
+
+def fixture_expected(name):
+    with open(fixture_paths(name)[3]) as f:
+        return json.load(f)
 
 
 class ClockSampler:
@@ -134,14 +170,30 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
-# ---- work model (DESIGN.md section "Kernels and rooflines") ---------------------------------------------------
+# ---- work model -------------------------------------------------------
 MODMUL_OPS = 136          # 32x32->64 multiply-adds per 254-bit Montgomery product (128 wide + 8 quotient digits)
 G1_MADD_MODMULS = 10      # XYZZ mixed addition: 8M + 2S over Fq
 G2_MADD_MODMULS = 28      # the same over Fq2: 8 x 3 (Karatsuba) + 2 x 2
+G1_ADD_MODMULS = 14       # full XYZZ addition (bucket reduction)
+G2_ADD_MODMULS = 42
 NTT_BYTES_PER_POINT = 384  # H pipeline, strict: 6 transforms x (32 B read + 32 B write) per domain point
 
-
 H_TABLE = {"auto": 0, "on": 1, "off": -1}
+
+
+def step_work(n, logn, n_coefs, stats):
+    """Algorithmic modmuls of one prove, by phase: accumulations = one mixed addition per non-zero
+    digit; transforms = 6 x (n/2) log2 n butterflies + 3n coset factors; reductions = 2 full additions per bucket;
+    r1cs + join = one product per coefficient, n for C = A.B, 2n for the join and de-Montgomery."""
+    acc = sum(G1_MADD_MODMULS * stats[k]["additions"] for k in ("A", "B1", "C", "H")) + G2_MADD_MODMULS * stats["B2"]["additions"]
+    ntt = 6 * (n // 2) * logn + 3 * n
+    red = 0
+    for k in ("A", "B1", "B2", "C", "H"):
+        windows = 1 if stats[k].get("tabled") else stats[k]["W"]
+        buckets = windows << (stats[k]["c"] - 1)
+        red += 2 * buckets * (G2_ADD_MODMULS if k == "B2" else G1_ADD_MODMULS)
+    other = n_coefs + n + 2 * n
+    return {"accumulate": acc, "transforms": ntt, "reductions": red, "r1cs_join": other}
 
 
 def measured_traffic(workload):
@@ -161,7 +213,7 @@ def measured_peaks():
         return {}
 
 
-def dist_setup(n_gpus):
+def dist_setup():
     """-> (rank, world, local_rank, dist module or None)"""
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -176,235 +228,355 @@ def dist_setup(n_gpus):
     return 0, 1, 0, None
 
 
-def run_b200(args):
-    import torch
-    rank, world, local, dist = dist_setup(args.gpus)
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the prover has no CPU fallback")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    pkg = load_pkg()
-    nv, npub, ncons, desc = WORKLOADS[args.workload]
-    if rank == 0:
-        fixture(args.workload)          # one rank generates, the others read the cache
-    if dist:
-        dist.barrier()
-    zkey, wtns = fixture(args.workload, rank)
+class Ctx:
+    """what every measurement needs: torch, the package, rank layout, collectives"""
 
-    t_open = time.perf_counter()
-    shard = args.mode in ("shard", "shard-rep") and world > 1
-    dist_ntt = args.mode == "shard"     # coset transforms spread over the ranks too (one all-to-all per polynomial)
-    if shard:
-        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, shard_rank=rank, shard_count=world, h_table=H_TABLE[args.h_table])
-    else:
-        zk = pkg.ZKey(zkey, device=local, msm_c=args.msm_c, h_table=H_TABLE[args.h_table])
-    t_open = time.perf_counter() - t_open
-    zkey_len = len(zkey)
-    del zkey
-    pinned = torch.empty(len(wtns), dtype=torch.uint8).pin_memory()
-    pinned.copy_(torch.frombuffer(bytearray(wtns), dtype=torch.uint8))
+    def __init__(self, args):
+        import torch
+        self.torch = torch
+        self.rank, self.world, self.local, self.dist = dist_setup()
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the prover has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.pkg = load_pkg()
+        self.args = args
+        self._peak = None
 
-    def sync_all():
-        torch.cuda.synchronize(dev)
-        if dist:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
+    def sync_all(self):
+        self.torch.cuda.synchronize(self.dev)
+        if self.dist:
+            self.dist.barrier()
+        self.torch.cuda.synchronize(self.dev)
 
-    def max_over_ranks(x):
-        if not dist:
+    def max_over_ranks(self, x):
+        if not self.dist:
             return x
-        t = torch.tensor([x], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
         return float(t.item())
 
-    # sharded mode: ONE proof over all ranks (base-range shards of sections 5-9, the H pipeline replicated, one
-    # NCCL all-gather of 768-byte partials, every rank finalises); pinned r,s so all ranks agree
-    R_PIN, S_PIN = 0x1234567 << 200, 0x7654321 << 190
+    def pinned(self, data):
+        t = self.torch.empty(len(data), dtype=self.torch.uint8).pin_memory()
+        t.copy_(self.torch.frombuffer(bytearray(data), dtype=self.torch.uint8))
+        return t
 
-    def step_loaded():
-        if shard and dist_ntt:
-            return pkg.prove_sharded_distributed(zk, None, r=R_PIN, s=S_PIN)
-        if shard:
-            return zk.combine(pkg.all_gather_partials(zk.prove_partial()), r=R_PIN, s=S_PIN)
-        return zk.prove_loaded()
+    def int_peak(self):
+        """wide multiply-adds per second of this GPU, measured now: the best of the carry-chain microbenchmarks (one
+        chain per thread, four independent chains per thread) and of dependent Montgomery products x 136"""
+        if self._peak is None:
+            one = self.pkg.bench_int_pipe(1)
+            four = self.pkg.bench_int_pipe(3)
+            modmul = self.pkg.bench_int_pipe(2)
+            self._peak = {"peak": max(one, four, modmul * MODMUL_OPS), "one_chain": one, "four_chains": four,
+                          "modmul_per_s": modmul, "modmul_x136": modmul * MODMUL_OPS}
+        return self._peak
 
-    def step_e2e():
-        if shard and dist_ntt:
-            return pkg.prove_sharded_distributed(zk, pinned, r=R_PIN, s=S_PIN)
-        if shard:
-            return pkg.prove_sharded(zk, pinned, r=R_PIN, s=S_PIN)
-        return zk.prove(pinned)
+    def fixture(self, name):
+        if self.rank == 0:
+            fixture(name, load=False)          # one rank generates, the others read the cache
+        if self.dist:
+            self.dist.barrier()
+        return fixture(name)
 
-    # ---- resident arm: witness in HBM before the timed region -----------------------------------------------------
-    zk.load_witness(pinned)
-    for _ in range(args.warmup):
-        proof, public = step_loaded()
-    clocks = ClockSampler(local)
-    phase = {}
-    acc_ms = {k: 0.0 for k in ("A", "B1", "B2", "C", "H")}
-    sync_all()
-    if rank == 0:
-        clocks.start()
-    launches0 = pkg.launch_count()
+
+def timed_steps(cx, fn, steps):
+    """K calls of fn bracketed by barrier + synchronize; device events and host clock, max over ranks -> seconds"""
+    torch = cx.torch
+    cx.sync_all()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     w0 = time.perf_counter()
-    for _ in range(args.steps):
-        proof, public = step_loaded()
+    out = None
+    for _ in range(steps):
+        out = fn()
+    e1.record()
+    torch.cuda.synchronize(cx.dev)
+    wall = time.perf_counter() - w0
+    return cx.max_over_ranks(max(e0.elapsed_time(e1) / 1e3, wall)), out
+
+
+def self_check(cx, zk, name, pinned, shard_step=None):
+    """untimed: (i) the proof under pinned r,s equals the closed-form known-trapdoor proof cached with the fixture, bit
+    for bit; (ii) a proof under fresh randomness passes the native pairing verifier"""
+    pkg = cx.pkg
+    exp = fixture_expected(name)
+    if shard_step:
+        proof, public = shard_step()
+    else:
+        proof, public = zk.prove(pinned, r=R_PIN, s=S_PIN)
+    bit_exact = json.loads(proof) == exp["proof"]
+    ok = None
+    if cx.args.verify and not shard_step:
+        p2, u2 = zk.prove(pinned)
+        with open(fixture_paths(name)[2]) as f:
+            ok = bool(pkg.verify(f.read(), u2, p2))
+    return bit_exact, ok, exp.get("maker")
+
+
+def measure(cx, name, steps, warmup, full=True):
+    """resident + end-to-end arms of one workload on every rank (replicas) -> result dict on rank 0"""
+    torch, pkg, args = cx.torch, cx.pkg, cx.args
+    nv, npub, ncons, desc = WORKLOADS[name]
+    zkey, wtns = cx.fixture(name)
+    t_open = time.perf_counter()
+    zk = pkg.ZKey(zkey, device=cx.local, msm_c=args.msm_c, h_table=H_TABLE[args.h_table])
+    t_open = time.perf_counter() - t_open
+    zkey_len, wtns_len = len(zkey), len(wtns)
+    del zkey
+    pinned = cx.pinned(wtns)
+    del wtns
+
+    # ---- resident arm: witness in HBM before the timed region ---------------------------------------------------
+    zk.load_witness(pinned)
+    for _ in range(warmup):
+        zk.prove_loaded()
+    clocks = ClockSampler(cx.local)
+    phase = {}
+    acc_ms = {k: 0.0 for k in ("A", "B1", "B2", "C", "H")}
+    if cx.rank == 0:
+        clocks.start()
+    launches0 = pkg.launch_count()
+
+    def step_loaded():
+        out = zk.prove_loaded()
         for k, v in zk.timings().items():
             phase[k] = phase.get(k, 0.0) + v
         for k, v in zk.accumulate_ms().items():
             acc_ms[k] += v
-    e1.record()
-    torch.cuda.synchronize(dev)
-    wall = time.perf_counter() - w0
-    dev_ms = e0.elapsed_time(e1)
-    launches = pkg.launch_count() - launches0
-    clk = clocks.stop() if rank == 0 else None
-    resident_s = max_over_ranks(max(dev_ms / 1e3, wall))
-    stats = zk.msm_stats()
+        return out
 
-    # ---- end-to-end arm: pinned host bytes in, JSON texts out, every step ------------------------------------------
-    for _ in range(max(1, args.warmup // 2)):
-        step_e2e()
-    sync_all()
-    w0 = time.perf_counter()
-    for _ in range(args.steps):
-        proof, public = step_e2e()
-    torch.cuda.synchronize(dev)
-    e2e_s = max_over_ranks(time.perf_counter() - w0)
+    resident_s, _ = timed_steps(cx, step_loaded, steps)
+    launches = pkg.launch_count() - launches0
+    clk = clocks.stop() if cx.rank == 0 else None
+    stats = zk.msm_stats()
+    trace = zk.trace()
+
+    # ---- end-to-end arm: pinned host bytes in, JSON texts out, every step -----------------------------------------
+    for _ in range(max(1, warmup // 2)):
+        zk.prove(pinned)
+    e2e_s, (proof, public) = timed_steps(cx, lambda: zk.prove(pinned), steps)
     d2h = len(proof) + len(public)
 
-    # ---- the same through ZKey.prove_stream: the next step's witness is copied (pinned host -> device) while this step
-    # computes (g16_witness_prefetch / g16_witness_commit); every step still has its own H2D copy and its own JSON out
+    # ---- the same through ZKey.prove_stream: witness i+1 is copied while proof i computes ---------------------------
     pipe_s = None
-    if not shard:
-        for _ in zk.prove_stream([pinned] * max(2, args.warmup // 2)):
+    if full:
+        for _ in zk.prove_stream([pinned] * max(2, warmup // 2)):
             pass
-        sync_all()
-        w0 = time.perf_counter()
-        for proof, public in zk.prove_stream([pinned] * args.steps):
-            pass
-        torch.cuda.synchronize(dev)
-        pipe_s = max_over_ranks(time.perf_counter() - w0)
 
-    # ---- self-check of the last proof (untimed): it must verify ------------------------------------------------------
-    ok = None
-    if rank == 0 and args.verify:
-        # g16_verify: the native host verifier (csrc/verify*.hpp), itself pinned on the reference's committed
-        # (vkey, public, proof) triples in tests/test_verify_native.py
-        with open(os.path.join(CACHE_DIR, args.workload + ".vkey.json")) as f:
-            ok = bool(pkg.verify(f.read(), public, proof))
+        def stream_all():
+            for out in zk.prove_stream([pinned] * steps):
+                pass
+            return out
+        pipe_s, _ = timed_steps(cx, stream_all, 1)
 
-    steps = args.steps
-    jobs = 1 if shard else world     # proofs finished per step over the whole job
-    g1_adds = sum(stats[k]["additions"] for k in ("A", "B1", "C", "H"))
-    g2_adds = stats["B2"]["additions"]
-    msm_points = 3 * nv - npub - 1 + zk.domain_size + nv
-    msm_ms = sum(phase[k] for k in ("msm_A", "msm_B1", "msm_B2", "msm_C", "msm_H")) / steps
-    acc_total_ms = sum(acc_ms.values()) / steps
-    int_ops = MODMUL_OPS * (G1_MADD_MODMULS * g1_adds + G2_MADD_MODMULS * g2_adds)
+    # ---- the H pipeline (r1cs + 6 transforms + join) timed alone, for its own roofline -----------------------------
+    ntt_alone_ms = None
+    if cx.rank == 0:
+        zk.load_witness(pinned)
+        zk.h_pipeline_dev()
+        t = []
+        for _ in range(5):
+            zk.h_pipeline_dev()
+            t.append(zk.timings()["ntt_pipeline"])
+        ntt_alone_ms = sorted(t)[len(t) // 2]
+
+    bit_exact = ok = maker = None
+    if cx.rank == 0:
+        bit_exact, ok, maker = self_check(cx, zk, name, pinned)
+
     out = None
-    if rank == 0:
-        peaks = measured_peaks()
-        traffic = measured_traffic(args.workload)
-        # the H section's fixed-base window table (opts.h_table): one bucket set of c+4-bit windows; told apart from the
-        # plain launch by the window width the run reports
-        plain_c = max(6, min(20, zk.domain_size.bit_length() - 1 - 5))     # msm_pick_c (csrc/msm.cuh)
+    if cx.rank == 0:
+        n, logn = zk.domain_size, zk.domain_size.bit_length() - 1
+        plain_c = max(6, min(20, logn - 5))                                # msm_pick_c (csrc/msm.cuh)
         h_tabled = not args.msm_c and stats["H"]["c"] > plain_c
-        if not h_tabled and "msm_accumulate_H_plain" in traffic:
-            traffic = dict(traffic, msm_accumulate_H=traffic["msm_accumulate_H_plain"])
-            traffic.pop("msm_accumulate", None)
-        acc_alg_bytes = 68 * g1_adds + 132 * g2_adds      # one base record + one 4-byte entry per mixed addition
+        stats["H"]["tabled"] = h_tabled
+        ms_step = resident_s / steps * 1e3
+        peak = cx.int_peak()
+        imad_peak = peak["peak"]
+        work = step_work(n, logn, zk.n_coefs, stats)
+        total_ops = MODMUL_OPS * sum(work.values())
         h_ms = acc_ms["H"] / steps
         h_ops = MODMUL_OPS * G1_MADD_MODMULS * stats["H"]["additions"]
-        imad_peak = pkg.bench_int_pipe(1)            # wide multiply-adds per second, measured on this GPU now
-        modmul_peak = pkg.bench_int_pipe(2)          # dependent-chain Montgomery products per second
-        hbm_peak = peaks.get("hbm_gbs")
-        ntt_gbs = NTT_BYTES_PER_POINT * zk.domain_size / (phase["ntt_pipeline"] / steps * 1e-3) / 1e9
+        acc_total_ms = sum(acc_ms.values()) / steps
+        msm_points = 3 * nv - npub - 1 + n + nv
+        msm_ms = sum(phase[k] for k in ("msm_A", "msm_B1", "msm_B2", "msm_C", "msm_H")) / steps
+        traffic = measured_traffic(name)
+        if not h_tabled and "msm_accumulate_H_plain" in traffic:
+            traffic = dict(traffic, msm_accumulate_H=traffic["msm_accumulate_H_plain"])
+        hbm_peak = measured_peaks().get("hbm_gbs")
+        ntt_ops = MODMUL_OPS * work["transforms"]
+        ntt_in_step_ms = phase["ntt_pipeline"] / steps
         out = {
-            "metric": "groth16_prove_constraints_per_s", "value": ncons * steps * jobs / resident_s,
-            "unit": "constraints/s", "n_gpus": world, "steps": steps, "warmup": args.warmup,
-            "ms_per_step": resident_s / steps * 1e3, "higher_is_better": True, "scaling": "strong" if shard else "weak",
+            "metric": "groth16_prove_constraints_per_s", "value": ncons * steps * cx.world / resident_s,
+            "unit": "constraints/s", "n_gpus": cx.world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32 limbs (256-bit Montgomery Fr/Fq/Fq2)", "data": "synthetic",
-            "config": {"workload": args.workload, "description": desc, "n_vars": nv, "n_public": npub,
-                       "n_constraints": ncons, "domain_size": zk.domain_size, "n_coefs": zk.n_coefs,
-                       "h_window_table": h_tabled,
-                       "zkey_bytes": zkey_len, "proofs_per_step": jobs,
-                       "parallelism": ("base-range shards x%d, %s, NCCL all-gather of 768 B partials"
-                                       % (world, "A/B/C transforms on ranks 0-%d + all-to-all of slices" % (min(world, 3) - 1)
-                                          if dist_ntt else "transforms replicated")) if shard else "replica-per-gpu",
+            "config": {"workload": name, "description": desc, "n_vars": nv, "n_public": npub,
+                       "n_constraints": ncons, "domain_size": n, "n_coefs": zk.n_coefs, "h_window_table": h_tabled,
+                       "zkey_bytes": zkey_len, "proofs_per_step": cx.world, "parallelism": "replica-per-gpu",
                        "l2": "inputs exceed L2 (bases + scalars > 1 GB touched per step); no flush",
                        "timing": "cuda events on the default stream around synchronous prove calls, max(event, host clock), max over ranks"},
             "prove_s": resident_s / steps,
             "msm_mpts_per_s": msm_points / (msm_ms * 1e-3) / 1e6 if msm_ms else None,
             "phases_ms": {k: v / steps for k, v in phase.items()},
             "msm": {k: dict(v, accumulate_ms=acc_ms[k] / steps) for k, v in stats.items()},
-            "trace_last_step_ms": zk.trace(),
+            "trace_last_step_ms": trace,
             "zkey_open_s": t_open,
             "clocks": clk,
-            "e2e_pipelined": ({"value": ncons * steps * jobs / pipe_s, "unit": "constraints/s",
-                               "ms_per_step": pipe_s / steps * 1e3, "h2d_bytes_per_step": len(wtns),
+            "e2e_pipelined": ({"value": ncons * steps * cx.world / pipe_s, "unit": "constraints/s",
+                               "ms_per_step": pipe_s / steps * 1e3, "h2d_bytes_per_step": wtns_len,
                                "api": "ZKey.prove_stream: witness i+1 copied while proof i computes"} if pipe_s else None),
-            "e2e": {"value": ncons * steps * jobs / e2e_s, "unit": "constraints/s", "ms_per_step": e2e_s / steps * 1e3,
-                    "h2d_bytes_per_step": len(wtns), "d2h_bytes_per_step": d2h},
+            "e2e": {"value": ncons * steps * cx.world / e2e_s, "unit": "constraints/s", "ms_per_step": e2e_s / steps * 1e3,
+                    "h2d_bytes_per_step": wtns_len, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(launches),
             # the dominant kernel = the bucket accumulation of the H MSM (one launch per step, the largest MSM at every
-            # config); CUDA events on its own stream around that launch.  The four witness-MSM launches overlap the
-            # transforms and each other, so their event times are not kernel durations: they are listed apart.
+            # config); CUDA events on its own stream around that launch
             "roofline": {"kernel": "msm_accumulate_kernel<G1>, H MSM launch (bucket accumulation; dominant kernel)",
                          "bound": "int", "achieved": h_ops / (h_ms * 1e-3) / 1e12 if h_ms else None,
                          "peak": imad_peak / 1e12, "unit": "T wide-IMAD/s",
                          "frac": (h_ops / (h_ms * 1e-3)) / imad_peak if h_ms else None,
                          "units_per_launch": stats["H"]["additions"], "ops_per_unit": MODMUL_OPS * G1_MADD_MODMULS,
                          "ms_per_launch": h_ms,
-                         "peak_source": "g16_bench_int_pipe(1): IMAD.WIDE.U32 carry chains, measured in this run "
+                         "peak_source": "max of g16_bench_int_pipe ops 1 (one carry chain per thread), 3 (four independent "
+                                        "chains) and 2 x 136 (dependent Montgomery products), measured in this run "
                                         "(MEASURED_PEAKS.json has no integer figure)",
-                         "modmul_peak_per_s": modmul_peak, "share_of_step": h_ms / (resident_s / steps * 1e3),
+                         "peak_candidates_T": {k: v / 1e12 for k, v in peak.items() if k not in ("peak", "modmul_per_s")},
+                         "modmul_peak_per_s": peak["modmul_per_s"], "share_of_step": h_ms / ms_step,
                          "algorithmic_bytes": 68 * stats["H"]["additions"],
                          "traffic": traffic.get("msm_accumulate_H", {}).get("bytes_per_launch"),
                          "traffic_source": traffic.get("msm_accumulate_H", {}).get("source")},
+            # every algorithmic wide multiply-add of the step over the step time: how well the whole proof uses the pipe
+            "roofline_step": {"bound": "int", "achieved": total_ops / (ms_step * 1e-3) / 1e12, "peak": imad_peak / 1e12,
+                              "unit": "T wide-IMAD/s", "frac": total_ops / (ms_step * 1e-3) / imad_peak,
+                              "modmuls": work, "ops_per_modmul": MODMUL_OPS},
             "roofline_all_accumulate": {"kernel": "all five msm_accumulate launches of a step (overlapped with other streams)",
-                                        "achieved": int_ops / (acc_total_ms * 1e-3) / 1e12 if acc_total_ms else None,
-                                        "frac": (int_ops / (acc_total_ms * 1e-3)) / imad_peak if acc_total_ms else None,
-                                        "sum_of_event_ms": acc_total_ms, "algorithmic_bytes": acc_alg_bytes,
+                                        "achieved": MODMUL_OPS * work["accumulate"] / (acc_total_ms * 1e-3) / 1e12 if acc_total_ms else None,
+                                        "frac": MODMUL_OPS * work["accumulate"] / (acc_total_ms * 1e-3) / imad_peak if acc_total_ms else None,
+                                        "sum_of_event_ms": acc_total_ms,
+                                        "algorithmic_bytes": 68 * sum(stats[k]["additions"] for k in ("A", "B1", "C", "H")) + 132 * stats["B2"]["additions"],
                                         "traffic": traffic.get("msm_accumulate", {}).get("bytes_per_step")},
-            "roofline_ntt": {"kernel": "ntt_pass_kernel x passes + r1cs/join (H pipeline)", "bound": "hbm",
-                             "achieved": ntt_gbs, "peak": hbm_peak, "unit": "GB/s",
-                             "frac": ntt_gbs / hbm_peak if hbm_peak else None,
-                             "traffic": (traffic["ntt_pass"]["bytes_per_launch"] * traffic["ntt_pass"]["launches_per_step"])
-                             if "ntt_pass" in traffic else None,
-                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "unavailable"},
+            # the six transforms: integer-bound at 256 bits (7 wide multiply-adds per byte against a machine balance of
+            # 1.4), so the integer peak is the yardstick; the HBM figure SURVEY 8(d) asked for is kept beside it
+            "roofline_ntt": {"kernel": "ntt_pass_kernel x passes (6 transforms of the H pipeline, timed alone)", "bound": "int",
+                             "achieved": ntt_ops / (ntt_alone_ms * 1e-3) / 1e12 if ntt_alone_ms else None,
+                             "peak": imad_peak / 1e12, "unit": "T wide-IMAD/s",
+                             "frac": ntt_ops / (ntt_alone_ms * 1e-3) / imad_peak if ntt_alone_ms else None,
+                             "ms_alone": ntt_alone_ms, "ms_in_step": ntt_in_step_ms,
+                             "hbm": {"achieved_gbs": NTT_BYTES_PER_POINT * n / (ntt_alone_ms * 1e-3) / 1e9 if ntt_alone_ms else None,
+                                     "peak_gbs": hbm_peak,
+                                     "frac": NTT_BYTES_PER_POINT * n / (ntt_alone_ms * 1e-3) / 1e9 / hbm_peak if hbm_peak and ntt_alone_ms else None,
+                                     "traffic": (traffic["ntt_pass"]["bytes_per_launch"] * traffic["ntt_pass"]["launches_per_step"])
+                                     if "ntt_pass" in traffic else None}},
+            "bit_exact": bit_exact, "bit_exact_against": "closed-form known-trapdoor proof for pinned r,s (fixture made by the %s generator)" % maker,
             "verified": ok,
         }
     zk.close()
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline(args.workload, budget_s=args.cpu_budget)
-    if rank == 0:
-        print(json.dumps(out), flush=True)
-    if dist:
-        dist.barrier()
-        dist.destroy_process_group()
+    del zk
+    torch.cuda.empty_cache()
+    return out, pinned
+
+
+def measure_strong(cx, name, steps, warmup, mode):
+    """ONE proof over all ranks: base-range shards of sections 5-9; mode "shard" spreads the coset transforms over the
+    ranks too (all-to-all of slices), "shard-rep" repeats them on every rank; 768-byte partials all-gathered."""
+    pkg, args = cx.pkg, cx.args
+    nv, npub, ncons, desc = WORKLOADS[name]
+    zkey, wtns = cx.fixture(name)
+    zk = pkg.ZKey(zkey, device=cx.local, msm_c=args.msm_c, shard_rank=cx.rank, shard_count=cx.world, h_table=H_TABLE[args.h_table])
+    del zkey
+    pinned = cx.pinned(wtns)
+    dist_ntt = mode == "shard"
+
+    def step_loaded():
+        if dist_ntt:
+            return pkg.prove_sharded_distributed(zk, None, r=R_PIN, s=S_PIN)
+        return zk.combine(pkg.all_gather_partials(zk.prove_partial()), r=R_PIN, s=S_PIN)
+
+    def step_e2e():
+        if dist_ntt:
+            return pkg.prove_sharded_distributed(zk, pinned, r=R_PIN, s=S_PIN)
+        return pkg.prove_sharded(zk, pinned, r=R_PIN, s=S_PIN)
+
+    zk.load_witness(pinned)
+    for _ in range(warmup):
+        step_loaded()
+    phase = {}
+
+    def timed():
+        out = step_loaded()
+        for k, v in zk.timings().items():
+            phase[k] = phase.get(k, 0.0) + v
+        return out
+    resident_s, _ = timed_steps(cx, timed, steps)
+    for _ in range(max(1, warmup // 2)):
+        step_e2e()
+    e2e_s, (proof, public) = timed_steps(cx, step_e2e, steps)
+    out = None
+    if cx.rank == 0:
+        bit_exact = json.loads(proof) == fixture_expected(name)["proof"]
+        ph = {k: v / steps for k, v in phase.items()}
+        bound = max((("transform", ph.get("r1cs_eval", 0) + ph.get("ntt_pipeline", 0)), ("H accumulate", ph.get("msm_H", 0)),
+                     ("witness MSMs", max(ph.get(k, 0) for k in ("msm_A", "msm_B1", "msm_B2", "msm_C")))), key=lambda kv: kv[1])
+        out = {"mode": mode, "workload": name, "n_gpus": cx.world, "scaling": "strong", "ms_per_proof": resident_s / steps * 1e3,
+               "value": ncons * steps / resident_s, "unit": "constraints/s",
+               "e2e_ms_per_proof": e2e_s / steps * 1e3, "phases_ms_rank0": ph, "bounded_by_rank0": bound[0], "bit_exact": bit_exact,
+               "parallelism": "base-range shards x%d, %s, NCCL all-gather of 768 B partials"
+                              % (cx.world, "coset transforms spread over the ranks + exchange of slices" if dist_ntt else "transforms replicated")}
+    zk.close()
+    return out
+
+
+def run_b200(args):
+    cx = Ctx(args)
+    name = args.workload
+    if args.mode != "replica" and cx.world > 1:
+        out = measure_strong(cx, name, args.steps, args.warmup, args.mode)
+        if cx.rank == 0:
+            nv, npub, ncons, desc = WORKLOADS[name]
+            line = {"metric": "groth16_prove_constraints_per_s", "value": out["value"], "unit": "constraints/s", "n_gpus": cx.world,
+                    "steps": args.steps, "warmup": args.warmup, "ms_per_step": out["ms_per_proof"], "higher_is_better": True,
+                    "scaling": "strong", "vs_baseline": None, "dtype": "u32 limbs (256-bit Montgomery Fr/Fq/Fq2)", "data": "synthetic",
+                    "config": {"workload": name, "description": desc, "n_vars": nv, "n_public": npub, "n_constraints": ncons,
+                               "parallelism": out["parallelism"]}, "strong": out}
+            print(json.dumps(line), flush=True)
+    else:
+        out, pinned = measure(cx, name, args.steps, args.warmup)
+        if cx.world > 1 and args.strong:
+            # the same workload as ONE proof over all ranks, both transform placements
+            strong = [measure_strong(cx, name, max(3, args.steps // 2), 3, m) for m in ("shard-rep", "shard")]
+            if cx.rank == 0:
+                best = min(strong, key=lambda s: s["ms_per_proof"])
+                out["strong"] = dict(best, speedup_vs_one_gpu_replica=out["ms_per_step"] / best["ms_per_proof"], modes=strong)
+        if cx.rank == 0 and cx.world == 1:
+            if not args.no_cpu_baseline:
+                out["cpu_baseline"] = cpu_baseline(name, budget_s=args.cpu_budget)
+            per = [w for w in args.per_config.split(",") if w and w != "none" and w != name]
+            out["per_config"] = []
+            for w in per:
+                t0 = time.perf_counter()
+                try:
+                    r, _ = measure(cx, w, max(3, args.steps // 3), 3, full=False)
+                    keep = ("value", "unit", "ms_per_step", "steps", "config", "e2e", "roofline", "roofline_step", "roofline_ntt",
+                            "phases_ms", "trace_last_step_ms", "bit_exact", "verified", "zkey_open_s", "msm_mpts_per_s", "gpu_launches")
+                    r = {k: r[k] for k in keep}
+                    r["wall_s_including_fixture"] = time.perf_counter() - t0
+                    out["per_config"].append(r)
+                except Exception as e:           # a config that does not fit this box is reported, not fatal
+                    out["per_config"].append({"config": {"workload": w}, "error": repr(e)})
+        if cx.rank == 0:
+            print(json.dumps(out), flush=True)
+    if cx.dist:
+        cx.dist.barrier()
+        cx.dist.destroy_process_group()
 
 
 # ---- CPU arm: the oracle port (oracle/c/oracle.c) on the host cores ---------------------------------------------
-def sample_workload(name, per_step_budget_s):
-    """A bounded sample of `name` for the CPU: the workload itself if one prove fits the per-step budget, else a
-    SYNTH-1 circuit of the same shape (same wire classes, same coefficients per constraint) with fewer constraints.
-    The metric is a rate (constraints/s), so the sample's rate is reported as is."""
-    from oracle import cport
+def sample_workload(name, fit_constraints):
+    """A bounded sample of `name` for the CPU: a SYNTH-1 circuit of the same shape (same wire classes, same coefficients
+    per constraint) with about fit_constraints constraints.  The metric is a rate (constraints/s)."""
     nv, npub, ncons, _ = WORKLOADS[name]
-    # calibrate on 2^17 constraints (about a second)
-    cal = "cpu-cal-131000"
-    WORKLOADS[cal] = (125000, npub, 131000, "calibration sample")
-    zk, wt = fixture(cal)
-    t = time.perf_counter()
-    cport.prove_points(zk, wt, 1, 2)
-    rate = 131000 / (time.perf_counter() - t)
-    fit = int(rate * per_step_budget_s)
-    if fit >= ncons:
-        return name, "1 full prove of the workload per step"
-    lg = max(17, min(fit, ncons).bit_length() - 1)
+    lg = max(17, min(fit_constraints, ncons).bit_length() - 1)
     sc = (1 << lg) - 72                       # just under a power of two, like the reference's circuits
     sv = int(sc * nv / ncons)
     sname = "%s-sample-%d" % (name, sc)
@@ -412,25 +584,51 @@ def sample_workload(name, per_step_budget_s):
     return sname, "1 prove of a %d-constraint / %d-wire SYNTH-1 circuit of the same shape per step (workload has %d)" % (sc, sv, ncons)
 
 
-def cpu_prove_loop(sname, steps, warmup):
+def cpu_plan(name, steps, warmup, budget_s, maker):
+    """-> (workload to prove, description, calibrated seconds per prove, fixture bytes).  The full workload whenever
+    (steps + warmup) proves of it fit the budget; calibrated on the SECOND prove of a 2^17 circuit (the first call of
+    a process may build the library)."""
     from oracle import cport
-    zk, wt = fixture(sname)
+    cport.lib()
+    nv, npub, ncons, _ = WORKLOADS[name]
+    cal = "cpu-cal-131000"
+    WORKLOADS[cal] = (125000, npub, 131000, "calibration sample")
+    zk, wt = fixture(cal, maker)
+    cport.prove_points(zk, wt, 1, 2)
+    t = time.perf_counter()
+    cport.prove_points(zk, wt, 1, 2)
+    rate = 131000 / (time.perf_counter() - t)
+    # CPU Pippenger gets faster per constraint as n grows, so this estimate errs towards the full workload
+    if ncons / rate * (steps + warmup) <= budget_s:
+        return name, "1 full prove of the workload per step (%d constraints)" % ncons
+    fit = int(rate * budget_s / max(1, steps + warmup))
+    return sample_workload(name, fit)
+
+
+def cpu_prove_loop(sname, steps, warmup, maker):
+    from oracle import cport
+    zk, wt = fixture(sname, maker)
+    pts = None
     for _ in range(warmup):
-        cport.prove_points(zk, wt, 1, 2)
+        pts = cport.prove_points(zk, wt, R_PIN, S_PIN)
     t = time.perf_counter()
     for _ in range(steps):
-        pts = cport.prove_points(zk, wt, 1, 2)
-    return time.perf_counter() - t, pts, cport.last_timings(), cport.threads()
+        pts = cport.prove_points(zk, wt, R_PIN, S_PIN)
+    dt = time.perf_counter() - t
+    exp = fixture_expected(sname)["proof"]
+    return dt, proof_object(pts) == exp, cport.last_timings(), cport.threads()
 
 
-def cpu_baseline(name, budget_s=25.0):
-    """cpu_baseline leg of the default run: ~budget_s of CPU work on a bounded sample, rank 0, N=1."""
-    sname, what = sample_workload(name, budget_s)
-    dt, _, phases, threads = cpu_prove_loop(sname, 1, 0)
+def cpu_baseline(name, budget_s=30.0):
+    """cpu_baseline leg of the default run: the oracle port on the host cores, rank 0, N=1: one prove of the full
+    workload when it fits the budget (c2-layer-one: about 3 s on 16 cores), else of a bounded sample of it."""
+    sname, what = cpu_plan(name, 2, 0, budget_s, "gpu")
+    dt, exact, phases, threads = cpu_prove_loop(sname, 1, 1 if sname == name else 0, "gpu")
     return {"value": WORKLOADS[sname][2] / dt, "unit": "constraints/s", "cores": threads, "kind": "port",
-            "sample": what, "seconds": dt, "phases_s": phases,
-            "note": "oracle/c/oracle.c (C restatement of the snarkjs/rapidsnark algorithm, pthreads); rapidsnark and "
-                    "snarkjs cannot be installed offline"}
+            "sample": what, "seconds": dt, "phases_s": phases, "bit_exact": exact,
+            "note": "oracle/c/oracle.c (C restatement of the snarkjs/rapidsnark algorithm, pthreads, plain unsigned __int128 field "
+                    "arithmetic); rapidsnark and snarkjs cannot be installed offline, so every GPU/CPU ratio here is against "
+                    "this port, not against the reference's own provers"}
 
 
 def run_reference(args):
@@ -438,9 +636,8 @@ def run_reference(args):
     if rank != 0:
         return
     nv, npub, ncons, desc = WORKLOADS[args.workload]
-    per_step = max(2.0, args.ref_budget / max(1, args.steps + args.warmup))
-    sname, what = sample_workload(args.workload, per_step)
-    dt, pts, phases, threads = cpu_prove_loop(sname, args.steps, args.warmup)
+    sname, what = cpu_plan(args.workload, args.steps, args.warmup, args.ref_budget, "cpu")
+    dt, exact, phases, threads = cpu_prove_loop(sname, args.steps, args.warmup, "cpu")
     sc = WORKLOADS[sname][2]
     v = sc * args.steps / dt
     print(json.dumps({
@@ -448,9 +645,12 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 limbs (256-bit Montgomery)",
         "data": "synthetic",
-        "config": {"workload": args.workload, "description": desc, "n_vars": nv, "n_public": npub, "n_constraints": ncons},
+        "config": {"workload": args.workload, "description": desc, "n_vars": nv, "n_public": npub, "n_constraints": ncons,
+                   "same_workload_as_gpu_arm": sname == args.workload},
         "cpu_baseline": {"value": v, "unit": "constraints/s", "cores": threads, "kind": "port", "sample": what,
-                         "phases_s": phases},
+                         "phases_s": phases, "bit_exact": exact,
+                         "note": "oracle/c/oracle.c on all host threads; fixture made on the host cores by oracle/c/synth1.h; "
+                                 "no repository CUDA library is loaded and the GPU is not used in this arm"},
         "e2e": {"value": v, "unit": "constraints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }), flush=True)
@@ -463,18 +663,20 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--per-config", default=DEFAULT_PER_CONFIG,
+                    help="N = 1: comma-separated larger workloads also measured in this run (fewer steps), or 'none'")
     ap.add_argument("--mode", default="replica", choices=["replica", "shard", "shard-rep"],
-                    help="N > 1: replica = one independent proof per GPU (weak scaling, default); shard = one proof "
-                         "over all GPUs (strong scaling): sections 5-9 split by base range, the A/B/C coset transforms on "
-                         "ranks 0-2 with an all-to-all of their slices, one all-gather of partial sums; shard-rep = the "
-                         "same with the transforms repeated on every rank (no slice exchange)")
+                    help="N > 1: replica = one independent proof per GPU (weak scaling, default; the run also reports ONE "
+                         "proof over all GPUs under 'strong'); shard / shard-rep = make the one-proof-over-all-GPUs "
+                         "measurement the headline (coset transforms spread over the ranks / repeated on every rank)")
+    ap.add_argument("--no-strong", dest="strong", action="store_false", help="N > 1: skip the strong-scaling block")
     ap.add_argument("--msm-c", type=int, default=0, help="Pippenger window bits (0 = automatic)")
     ap.add_argument("--h-table", default="auto", choices=sorted(H_TABLE),
                     help="fixed-base window table for the H section (auto = on when it fits in a quarter of free HBM)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", dest="verify", action="store_false")
-    ap.add_argument("--cpu-budget", type=float, default=25.0, help="seconds of CPU work for the cpu_baseline leg")
-    ap.add_argument("--ref-budget", type=float, default=150.0, help="seconds for the whole --impl reference run")
+    ap.add_argument("--cpu-budget", type=float, default=30.0, help="seconds of CPU work for the cpu_baseline leg")
+    ap.add_argument("--ref-budget", type=float, default=300.0, help="seconds for the whole --impl reference run")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

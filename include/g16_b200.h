@@ -174,7 +174,8 @@ int g16_last_trace(const g16_zkey* zk, double out[30]);
 /* cumulative number of this library's own kernel launches in this process (library kernels such as cub's are
  * not counted) */
 unsigned long long g16_launch_count(void);
-/* integer-pipe microbenchmark: op 0 = 32-bit IMAD, 1 = IMAD.WIDE.U32 (+carry chain), 2 = Montgomery products.
+/* integer-pipe microbenchmark: op 0 = 32-bit IMAD, 1 = IMAD.WIDE.U32 on ONE carry chain per thread, 2 = dependent
+ * Montgomery products, 3 = IMAD.WIDE.U32 on FOUR independent carry chains per thread (the roofline denominator).
  * Returns achieved ops per second over the whole device (op 2: field products per second). */
 int g16_bench_int_pipe(int op, double* ops_per_s);
 

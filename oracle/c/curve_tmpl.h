@@ -184,3 +184,92 @@ static void CN(msm)(CN(jac) * out, const uint8_t* bases, const uint8_t* scalars,
     for (int t = 0; t < T; t++) CN(add)(out, out, &part[t]);
     free(part);
 }
+
+/* ---- fixed-base scalar multiplication k*G (used by the SYNTH-1 fixture generator in synth1.h only) ----------------
+ * FB_W windows of FB_C bits; table[w][d-1] = d * 2^(FB_C w) * G in affine form, so k*G is at most FB_W mixed
+ * additions.  Results are brought back to affine in batches with one inversion each (Montgomery's trick). */
+#ifndef FB_C
+#define FB_C 13
+#define FB_W 20
+#define FB_ROW ((1u << FB_C) - 1)
+#endif
+typedef struct { FE x, y; } CN(xy);
+
+/* out[i] = affine form of in[i] (all-zero for the identity); scratch holds n elements */
+static void CN(batch_to_affine)(CN(xy) * out, const CN(jac) * in, size_t n, FE* scratch) {
+    FE acc, inv;
+    FN(one)(&acc);
+    for (size_t i = 0; i < n; i++) {
+        if (CN(is_inf)(&in[i])) continue;
+        scratch[i] = acc;
+        FN(mul)(&acc, &acc, &in[i].z);
+    }
+    FN(inv)(&inv, &acc);
+    for (size_t i = n; i-- > 0;) {
+        if (CN(is_inf)(&in[i])) { memset(&out[i], 0, sizeof(out[i])); continue; }
+        FE zi, zi2, zi3;
+        FN(mul)(&zi, &inv, &scratch[i]);
+        FN(mul)(&inv, &inv, &in[i].z);
+        FN(sqr)(&zi2, &zi);
+        FN(mul)(&zi3, &zi2, &zi);
+        FN(mul)(&out[i].x, &in[i].x, &zi2);
+        FN(mul)(&out[i].y, &in[i].y, &zi3);
+    }
+}
+
+typedef struct { CN(xy) * table; CN(aff) gen; } CN(fb_ctx);
+static void CN(fb_table_range)(size_t lo, size_t hi, void* p) {
+    CN(fb_ctx)* c = (CN(fb_ctx)*)p;
+    CN(jac)* row = (CN(jac)*)malloc(FB_ROW * sizeof(CN(jac)));
+    FE* scratch = (FE*)malloc(FB_ROW * sizeof(FE));
+    for (size_t w = lo; w < hi; w++) {
+        CN(jac) base;
+        CN(from_affine)(&base, &c->gen);
+        for (size_t i = 0; i < FB_C * w; i++) CN(dbl)(&base, &base);
+        row[0] = base;
+        for (size_t d = 1; d < FB_ROW; d++) CN(add)(&row[d], &row[d - 1], &base);
+        CN(batch_to_affine)(c->table + w * FB_ROW, row, FB_ROW, scratch);
+    }
+    free(row);
+    free(scratch);
+}
+static CN(xy) * CN(fb_table)(const CN(aff) * gen) {
+    CN(fb_ctx) c;
+    c.table = (CN(xy)*)malloc((size_t)FB_W * FB_ROW * sizeof(CN(xy)));
+    c.gen = *gen;
+    par_range(FB_W, 0, CN(fb_table_range), &c);
+    return c.table;
+}
+
+/* out[i] = scalars[i] * G as a zkey record (affine, Montgomery, all-zero = infinity); scalars: 32 B LE standard form */
+typedef struct { const CN(xy) * table; const uint8_t* scalars; uint8_t* out; } CN(fbm_ctx);
+static void CN(fb_mul_range)(size_t lo, size_t hi, void* p) {
+    CN(fbm_ctx)* c = (CN(fbm_ctx)*)p;
+    enum { BATCH = 1024 };
+    CN(jac)* acc = (CN(jac)*)malloc(BATCH * sizeof(CN(jac)));
+    CN(xy)* aff = (CN(xy)*)malloc(BATCH * sizeof(CN(xy)));
+    FE* scratch = (FE*)malloc(BATCH * sizeof(FE));
+    for (size_t b = lo; b < hi; b += BATCH) {
+        size_t m = hi - b < BATCH ? hi - b : BATCH;
+        for (size_t i = 0; i < m; i++) {
+            uint64_t s[4];
+            memcpy(s, c->scalars + 32 * (b + i), 32);
+            CN(set_inf)(&acc[i]);
+            for (int w = 0; w < FB_W; w++) {
+                uint32_t d = CN(window)(s, w * FB_C, FB_C);
+                if (!d) continue;
+                const CN(xy)* q = c->table + (size_t)w * FB_ROW + (d - 1);
+                CN(madd)(&acc[i], &acc[i], &q->x, &q->y);
+            }
+        }
+        CN(batch_to_affine)(aff, acc, m, scratch);
+        memcpy(c->out + sizeof(CN(xy)) * b, aff, m * sizeof(CN(xy)));
+    }
+    free(acc);
+    free(aff);
+    free(scratch);
+}
+static void CN(fb_mul)(const CN(xy) * table, const uint8_t* scalars, size_t n, uint8_t* out) {
+    CN(fbm_ctx) c = {table, scalars, out};
+    par_range(n, 256, CN(fb_mul_range), &c);
+}

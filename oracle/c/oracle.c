@@ -625,3 +625,6 @@ EXPORT int orc_prove(const uint8_t* zkey, size_t zlen, const uint8_t* wtns, size
     g_times[7] = now_s() - t_all;
     return 0;
 }
+
+/* ---- SYNTH-1 fixture generator (orc_synth_sizes, orc_synth_write) ------------------------------------------------ */
+#include "synth1.h"

@@ -1,5 +1,6 @@
 """ctypes binding of the C oracle (oracle/c/oracle.c).  ORACLE CODE: test infrastructure / timed CPU baseline only."""
 import ctypes
+import hashlib
 import os
 import subprocess
 
@@ -12,7 +13,7 @@ _lib = None
 
 
 def build(force=False):
-    src = [os.path.join(_DIR, f) for f in ("oracle.c", "curve_tmpl.h", "Makefile")]
+    src = [os.path.join(_DIR, f) for f in ("oracle.c", "curve_tmpl.h", "synth1.h", "Makefile")]
     stale = not os.path.exists(_LIB) or any(os.path.getmtime(s) > os.path.getmtime(_LIB) for s in src)
     if force or stale:
         # -march=native is per machine: a library built in the build container may not run on the GPU box's CPU,
@@ -26,11 +27,15 @@ def lib():
     if _lib is None:
         marker = _LIB + ".host"
         host = open("/proc/cpuinfo").read().split("flags")[1].split("\n")[0] if os.path.exists("/proc/cpuinfo") else ""
-        tag = str(hash(host))
+        # sha256, not hash(): str hashes are salted per process, and a tag that never matches rebuilt the library in
+        # every process (inside the first timed call of bench.py's calibration)
+        tag = hashlib.sha256(host.encode()).hexdigest()
         if not os.path.exists(_LIB) or not os.path.exists(marker) or open(marker).read() != tag:
             build(force=True)
             with open(marker, "w") as f:
                 f.write(tag)
+        else:
+            build()
         L = ctypes.CDLL(_LIB)
         L.orc_threads.restype = ctypes.c_int
         L.orc_set_threads.argtypes = [ctypes.c_int]
@@ -42,6 +47,10 @@ def lib():
         L.orc_h_scalars.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
         L.orc_prove.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_char_p,
                                 ctypes.c_char_p, ctypes.c_void_p]
+        L.orc_synth_sizes.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p,
+                                      ctypes.c_void_p]
+        L.orc_synth_write.argtypes = [ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_uint64,
+                                      ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -131,3 +140,60 @@ def last_timings():
     t = (ctypes.c_double * 8)()
     lib().orc_last_timings(t)
     return dict(zip(["abc", "ntt_join", "msm_A", "msm_B1", "msm_B2", "msm_C", "msm_H", "total"], list(t)))
+
+
+class Synth:
+    """SYNTH-1 fixture on the host cores (oracle/c/synth1.h): same bytes as oracle.factory and as the CUDA generator
+    (zk-proof-of-assets_b200/csrc/synth.cu), made without the GPU or any of the repository's CUDA libraries."""
+
+    def __init__(self, n_vars, n_public, n_constraints, circuit_seed=1, trapdoor_seed=2):
+        zb, wb, dom = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint32()
+        if lib().orc_synth_sizes(n_vars, n_public, n_constraints, ctypes.addressof(zb), ctypes.addressof(wb), ctypes.addressof(dom)):
+            raise ValueError("SYNTH-1 needs nVars >= nPublic+21, nConstraints >= nVars-1 and a domain of at most 2^27")
+        self.n_vars, self.n_public, self.n_constraints = n_vars, n_public, n_constraints
+        self.circuit_seed, self.trapdoor_seed = circuit_seed, trapdoor_seed
+        self.zkey_bytes, self.wtns_bytes, self.domain_size = zb.value, wb.value, dom.value
+        self._vk = self._sums = None
+
+    def write(self, want_zkey=True, want_wtns=True):
+        """-> (zkey bytearray | None, wtns bytearray | None)"""
+        zk = bytearray(self.zkey_bytes) if want_zkey else None
+        wt = bytearray(self.wtns_bytes) if want_wtns else None
+        vk = ctypes.create_string_buffer(64 + 3 * 128 + (self.n_public + 1) * 64) if want_zkey else None
+        sums = ctypes.create_string_buffer(128)
+        if lib().orc_synth_write(self.n_vars, self.n_public, self.n_constraints, self.circuit_seed, self.trapdoor_seed,
+                                 _addr(zk) if zk is not None else None, _addr(wt) if wt is not None else None,
+                                 ctypes.addressof(vk) if vk is not None else None, ctypes.addressof(sums)):
+            raise ValueError("orc_synth_write failed")
+        if vk is not None:
+            self._vk = vk.raw
+        self._sums = [int.from_bytes(sums.raw[32 * i:32 * i + 32], "little") for i in range(4)]
+        return zk, wt
+
+    def vkey(self):
+        """snarkjs-style verification key dict (decimal strings); write() with a zkey first."""
+        if self._vk is None:
+            self.write(True, False)
+        v = [str(int.from_bytes(self._vk[32 * i:32 * i + 32], "little")) for i in range(len(self._vk) // 32)]
+
+        def g2(o):
+            return [[v[o], v[o + 1]], [v[o + 2], v[o + 3]], ["1", "0"]]
+
+        ic = [[v[14 + 2 * i], v[15 + 2 * i], "1"] for i in range(self.n_public + 1)]
+        return {"protocol": "groth16", "curve": "bn128", "nPublic": self.n_public, "vk_alpha_1": [v[0], v[1], "1"],
+                "vk_beta_2": g2(2), "vk_gamma_2": g2(6), "vk_delta_2": g2(10), "IC": ic}
+
+    def expected(self, r, s):
+        """closed-form proof for pinned r,s from the trapdoor and the four exponent sums: three scalar multiplications,
+        independent of any MSM/NTT code -> (pi_a, pi_b, pi_c) affine ints"""
+        from . import factory
+        if self._sums is None:
+            self.write(False, False)
+        At, Bt, Ct, priv = self._sums
+        td = factory.Trapdoor(self.trapdoor_seed)
+        R = bn.R
+        dinv = bn.inv_mod(td.delta, R)
+        ea = (td.alpha + At + r * td.delta) % R
+        eb = (td.beta + Bt + s * td.delta) % R
+        ec = ((priv + At * Bt - Ct) * dinv + s * ea + r * eb - r * s % R * td.delta) % R
+        return bn.G1.mul(bn.G1_GEN, ea), bn.G2.mul(bn.G2_GEN, eb), bn.G1.mul(bn.G1_GEN, ec)

@@ -85,3 +85,37 @@ def test_c_prove_error_codes(small_fixture):
         cport.prove_points(f["zkey_bytes"], binfile.write_wtns(f["w"], prime=Q), 1, 2)
     with pytest.raises(ValueError, match="code 6"):
         cport.prove_points(f["zkey_bytes"][:3000], f["wtns_bytes"], 1, 2)
+
+
+def test_c_fixture_generator_matches_python_factory():
+    """oracle/c/synth1.h (host-core SYNTH-1 generator the reference arm of bench.py uses) writes the bytes of the
+    Python factory, and its closed-form proof equals the factory's."""
+    for nv, npub, nc in ((85, 2, 100), (300, 1, 310), (1500, 13, 1600)):
+        circ = factory.SynthCircuit(n_vars=nv, n_public=npub, n_constraints=nc, seed=0xB2000001)
+        td = factory.Trapdoor(0xB2000002)
+        zk, vkey = factory.setup(circ, td)
+        w = circ.witness()
+        sy = cport.Synth(nv, npub, nc, 0xB2000001, 0xB2000002)
+        z2, w2 = sy.write()
+        assert bytes(z2) == binfile.write_zkey(zk)
+        assert bytes(w2) == binfile.write_wtns(w)
+        assert sy.vkey() == vkey
+        r, s = 0x1234567 << 200, 0x7654321 << 190
+        want = factory.closed_form_proof(circ, w, td, r % R, s % R)
+        assert sy.expected(r % R, s % R) == want
+        assert cport.prove_points(bytes(z2), bytes(w2), r, s) == want
+
+
+def test_cport_host_tag_is_stable_across_processes():
+    """the marker that decides whether liboracle.so is rebuilt must not depend on Python's per-process hash salt"""
+    import subprocess
+    import sys
+    code = "import sys; sys.path.insert(0, %r); from oracle import cport; cport.lib(); print(open(cport._LIB + '.host').read())"
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    a = subprocess.run([sys.executable, "-c", code % root], capture_output=True, text=True, check=True).stdout
+    before = os.path.getmtime(cport._LIB)
+    b = subprocess.run([sys.executable, "-c", code % root], capture_output=True, text=True, check=True,
+                       env=dict(os.environ, PYTHONHASHSEED="12345")).stdout
+    assert a == b and len(a.strip()) == 64
+    assert os.path.getmtime(cport._LIB) == before      # second process did not rebuild

@@ -263,6 +263,34 @@ __global__ void int_pipe_kernel(int op, int iters, uint32_t seed, uint32_t* out)
         uint32_t r = 0;
         for (int k = 0; k < 8; k++) r ^= acc[k];
         out[t] = r;
+    } else if (op == 3) {
+        // four INDEPENDENT carry-chain accumulators per thread (op 1 has one: each row waits for the carry of the one
+        // before), i.e. the instruction-level parallelism a Montgomery product offers the scheduler
+        uint32_t a0[8], a1[8], a2[8], a3[8];
+        for (int k = 0; k < 8; k++) {
+            a0[k] = seed + t + k;
+            a1[k] = seed * 3 + t + k;
+            a2[k] = (seed ^ 0x55aa55aau) + t * 7 + k;
+            a3[k] = seed + t * 13 + k;
+        }
+        uint32_t x0 = seed * 3 + t, x1 = x0 ^ 0x9e3779b9u, x2 = x1 + 77, x3 = x2 * 5;
+        uint32_t y0 = seed + 12345, y1 = seed + 777, y2 = seed * 9 + 1, y3 = seed ^ 0xdeadbeefu;
+        for (int i = 0; i < iters; i++) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                uint32_t c0 = mad_row_c(a0, x0, x1, x2, x3, y0);
+                uint32_t c1 = mad_row_c(a1, x1, x2, x3, x0, y1);
+                uint32_t c2 = mad_row_c(a2, x2, x3, x0, x1, y2);
+                uint32_t c3 = mad_row_c(a3, x3, x0, x1, x2, y3);
+                y0 += c0 + 1;
+                y1 += c1 + 1;
+                y2 += c2 + 1;
+                y3 += c3 + 1;
+            }
+        }
+        uint32_t r = 0;
+        for (int k = 0; k < 8; k++) r ^= a0[k] ^ a1[k] ^ a2[k] ^ a3[k];
+        out[t] = r;
     } else {
         fe_t a = Fq::one(), b = Fq::r2();
         a.v[0] ^= t;
@@ -496,7 +524,8 @@ int g16_bench_int_pipe(int op, double* ops_per_s) {
         cudaEventElapsedTime(&ms, e0, e1);
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
-        double per_thread = op == 0 ? 64.0 * iters : op == 1 ? 64.0 * iters : 8.0 * iters;
+        // ops per thread: 0 = IMAD, 1 and 3 = wide multiply-adds (16 rows of 4 per iteration), 2 = Montgomery products
+        double per_thread = op == 2 ? 8.0 * iters : 64.0 * iters;
         *ops_per_s = per_thread * blocks * threads * reps / (ms * 1e-3);
         return (int)G16_OK;
     });

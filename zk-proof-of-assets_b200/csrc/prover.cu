@@ -5,9 +5,11 @@
 // rapidsnark Groth16::Prover::prove; reference call site scripts/g16_prove.sh:246-260.
 #include <fcntl.h>
 #include <sys/mman.h>
+#include <sys/random.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <cerrno>
 #include <chrono>
 #include <future>
 #include <cstdio>
@@ -272,9 +274,6 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     if (opts) o = *opts;
     else g16_opts_default(&o);
     set_device(o.device);
-    // G16_L2_FETCH=<32|64|128>: the device's L2 fetch granularity hint (experiment: the H accumulation reads 64-byte
-    // rows scattered over a table far larger than L2)
-    if (const char* e = std::getenv("G16_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(e));
     std::unique_ptr<g16_zkey> zk(new g16_zkey());
     G16_CUDA(cudaGetDevice(&zk->device));
     zk->shard_count = o.shard_count > 1 ? o.shard_count : 1;
@@ -653,11 +652,22 @@ static U256 reduce_scalar(U256 a) {
     while (u256_cmp(a, HFr::mod()) >= 0) a = HFr::raw_sub(a, HFr::mod());
     return a;
 }
-static U256 random_scalar() {  // row a14: uniform in Fr by rejection
-    std::random_device rd;
+// row a14: uniform in Fr by rejection, from the kernel's CSPRNG (getrandom(2); rapidsnark uses libsodium's
+// randombytes_buf, which reads the same source).  The zero-knowledge property of every proof rests on these bytes,
+// so a failing source is an error, never a fallback to a weaker generator.
+static U256 random_scalar() {
     for (;;) {
         U256 a;
-        for (int i = 0; i < 4; i++) a.v[i] = (uint64_t(rd()) << 32) | rd();
+        uint8_t* p = reinterpret_cast<uint8_t*>(a.v);
+        size_t got = 0;
+        while (got < 32) {
+            ssize_t k = getrandom(p + got, 32 - got, 0);
+            if (k < 0) {
+                if (errno == EINTR) continue;
+                throw std::runtime_error("getrandom failed: no entropy source for the blinding factors");
+            }
+            got += size_t(k);
+        }
         a.v[3] &= 0x3fffffffffffffffull;
         if (u256_cmp(a, HFr::mod()) < 0) return a;
     }
@@ -774,11 +784,21 @@ struct MappedFile {
     }
 };
 
+// written to a temporary beside the target and renamed, so that a concurrent reader (the workflow verifies right after
+// the prover exits, scripts/g16_verify.sh) or a crash never sees a truncated proof.json
 static void write_file(const char* path, const std::string& text) {
-    FILE* f = std::fopen(path, "wb");
+    std::string tmp = std::string(path) + ".tmp." + std::to_string((long)getpid());
+    FILE* f = std::fopen(tmp.c_str(), "wb");
     if (!f) throw std::runtime_error(std::string("cannot write ") + path);
     size_t w = std::fwrite(text.data(), 1, text.size(), f);
-    if (std::fclose(f) != 0 || w != text.size()) throw std::runtime_error(std::string("short write to ") + path);
+    if (std::fclose(f) != 0 || w != text.size()) {
+        std::remove(tmp.c_str());
+        throw std::runtime_error(std::string("short write to ") + path);
+    }
+    if (std::rename(tmp.c_str(), path) != 0) {
+        std::remove(tmp.c_str());
+        throw std::runtime_error(std::string("cannot rename onto ") + path);
+    }
 }
 
 }  // namespace g16
