@@ -5,18 +5,24 @@
 // Inputs are the zkey's own records: affine Montgomery bases (64 B G1, 128 B G2; all-zero = infinity) and 32-byte
 // little-endian standard-form scalars (wtns section 2, or the H scalars from the NTT pipeline).
 //
-// Pipeline of one MSM (all on one stream; two tiny device->host reads of counters):
-//   digits   : signed c-bit windows per scalar; only non-zero digits become (bucket key, point index|sign) entries
-//   sort     : cub radix sort of the entries by key = window * 2^(c-1) + (|digit| - 1)
-//   bounds   : run start/end per bucket from the sorted keys
-//   tasks    : a bucket with more than T entries is cut into tasks of <= T entries (load balance for
-//              witness-like scalars where one bucket can hold a quarter of all points); tasks sorted by length
+// Pipeline of one MSM.  Every step is enqueued on CUDA streams without the host ever reading a counter back: sizes
+// that depend on the scalars (entries, tasks, cut buckets) live in device memory, kernels that depend on them run
+// grid-stride loops over fixed grids, and buffers are sized from bounds known at reserve() time.
+//   count    : signed c-bit windows per scalar; every non-zero digit adds one to its bucket's counter
+//              (key = window * 2^(c-1) + |digit| - 1; warp-aggregated atomics: a quarter of a circom witness is 0/1)
+//   scan     : exclusive sum of the counters = first entry of every bucket (cub::DeviceScan; size nb is static)
+//   scatter  : the digits again; entry (point index | sign) goes to start[key] + cursor[key]++.  This is a counting
+//              sort by bucket: the order of entries INSIDE a bucket is arbitrary, which group addition does not care
+//              about (the affine result is the same point), so no radix sort and no key array exist.
+//   tasks    : a bucket with more than T entries is cut into tasks of <= T entries (T chosen on the device from the
+//              entry count); tasks are ordered longest-first by a counting sort on their length
 //   accumulate (the hot kernel, IMAD bound): one thread per task, XYZZ mixed additions, next point prefetched
 //   combine  : buckets that were cut are summed by one CTA each
 //   reduce   : per chunk of L buckets a running-sum gives sum (b+1) B_b; chunks are tree-summed per window
 //   windows  : the W window sums go to the host, which runs the Horner chain (c doublings per window)
 #pragma once
 #include <cub/cub.cuh>
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <stdexcept>
@@ -26,9 +32,7 @@
 
 namespace g16 {
 
-// entry values: bit 31 = negate the base, bit 30 = the index points into the merged-pair array (msm_pair_merge_kernel)
-constexpr uint32_t MSM_MERGED_FLAG = 0x40000000u;
-constexpr uint32_t MSM_INDEX_MASK = 0x3fffffffu;
+constexpr uint32_t MSM_INDEX_MASK = 0x7fffffffu;   // entry value: bit 31 = negate the base, bits 0-30 = base index
 
 static inline int msm_num_windows(int c) { return (255 + c - 1) / c; }
 
@@ -45,6 +49,7 @@ static inline int msm_pick_c(size_t n) {
 // block-wide tree sum of XYZZ points held one per thread; result in every thread.
 // The staging array is STATIC shared memory (16 KB G1 / 32 KB G2 at 128 threads): with an `extern __shared__`
 // byte array cast to pt*, nvcc 12.9 drops the first 16-byte store of `sh[threadIdx.x] = acc` (seen in the PTX).
+// Ends with a barrier, so it can be called again in a loop.
 template <class C, int THREADS>
 __device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
     __shared__ typename C::pt sh[THREADS];
@@ -59,22 +64,40 @@ __device__ __forceinline__ void block_sum_points(typename C::pt& acc) {
         __syncthreads();
     }
     acc = sh[0];
+    __syncthreads();
 }
+
+// counters of one MSM run, in device memory (MsmParams) and copied to the host with the window sums
+struct MsmParams {
+    uint32_t m;        // entries = non-zero digits = mixed additions
+    uint32_t T;        // max entries per task
+    uint32_t nt;       // tasks
+    uint32_t np;       // partial sums of cut buckets
+    uint32_t nblk;     // first-level combine blocks
+    uint32_t ncut;     // cut buckets
+    uint32_t pad[2];
+};
 
 #ifdef G16_MSM_INSTANTIATE   // the kernels are compiled in msm.cu only (one copy in the library, one module to load)
 // ---------------------------------------------------------------------------------------------------------
-// digits
+// digits: count and scatter
 // ---------------------------------------------------------------------------------------------------------
 // scalars: n x 8 u32 (standard form, < 2^254).  inf_mask: optional bitmask, bit i set = base i is infinity.
-static __global__ void msm_digits_kernel(const uint32_t* __restrict__ scalars, uint32_t n, const uint32_t* __restrict__ inf_mask,
-                                  int c, int W, uint32_t fold_n, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
-                                  unsigned long long* __restrict__ counter) {
-    // fold_n != 0 (fixed-base window table, see msm_window_table_kernel): every window shares ONE bucket set and the
-    // entry points at row w of the table, base index w * fold_n + i, which holds 2^(c w) * base_i
+// fold_n != 0 (fixed-base window table, see msm_window_table_kernel): every window shares ONE bucket set and the
+// entry points at row w of the table, base index w * fold_n + i, which holds 2^(c w) * base_i.
+// SCATTER = false: count[key]++.  SCATTER = true: vals[start[key] + cursor[key]++] = entry.
+// AGG: lanes of a warp that hit the same bucket in the same window share one atomic (witness-like scalars: the
+// digit-1 bucket of window 0 holds a quarter of all entries; without this its counter serialises the kernel).
+// Dense uniform scalars (the H MSM) have no such bucket and skip the match.
+template <bool SCATTER, bool AGG>
+static __global__ void __launch_bounds__(256)
+msm_digits_kernel(const uint32_t* __restrict__ scalars, uint32_t n, const uint32_t* __restrict__ inf_mask, int c, int W,
+                  uint32_t fold_n, uint32_t* __restrict__ count, const uint32_t* __restrict__ start,
+                  uint32_t* __restrict__ vals) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t half = 1u << (c - 1);
     const uint32_t mask = (1u << c) - 1;
-    uint32_t cnt = 0;
+    const uint32_t lane = threadIdx.x & 31;
     uint32_t s[8];
     bool live = i < n;
     if (live && inf_mask && ((inf_mask[i >> 5] >> (i & 31)) & 1)) live = false;
@@ -84,45 +107,44 @@ static __global__ void msm_digits_kernel(const uint32_t* __restrict__ scalars, u
         s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
         if ((s[0] | s[1] | s[2] | s[3] | s[4] | s[5] | s[6] | s[7]) == 0) live = false;
     }
-    // pass 1: count non-zero signed digits
-    if (live) {
-        uint32_t carry = 0;
-        for (int w = 0; w < W; w++) {
-            int bit = w * c, limb = bit >> 5, sh = bit & 31;
-            unsigned long long v = limb < 8 ? s[limb] : 0;
-            if (limb + 1 < 8) v |= (unsigned long long)s[limb + 1] << 32;
-            uint32_t d = (uint32_t)((v >> sh) & mask) + carry;
-            carry = d > half;
-            if (d != 0 && d != (1u << c)) cnt++;  // d == 2^c becomes digit 0 with a carry
-        }
-    }
-    // warp-aggregated reservation of output slots
-    uint32_t lane = threadIdx.x & 31;
-    uint32_t incl = cnt;
+    if (!AGG && !live) return;
+    if (!live) {
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
+        for (int k = 0; k < 8; k++) s[k] = 0;
     }
-    uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
-    unsigned long long base = 0;
-    if (lane == 31 && total) base = atomicAdd(counter, (unsigned long long)total);
-    base = __shfl_sync(0xffffffffu, base, 31);
-    if (!live || cnt == 0) return;
-    unsigned long long pos = base + (incl - cnt);
+    int nbits = 0;   // position of the scalar's highest set bit + 1
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+        if (s[k]) nbits = 32 * k + 32 - __clz(s[k]);
     uint32_t carry = 0;
     for (int w = 0; w < W; w++) {
         int bit = w * c, limb = bit >> 5, sh = bit & 31;
+        // nothing left above this window in any lane of the warp: done (bit and small wires end early)
+        if (AGG && !__any_sync(0xffffffffu, bit < nbits || carry)) break;
         unsigned long long v = limb < 8 ? s[limb] : 0;
         if (limb + 1 < 8) v |= (unsigned long long)s[limb + 1] << 32;
         uint32_t d = (uint32_t)((v >> sh) & mask) + carry;
         carry = d > half;
-        if (d == 0 || d == (1u << c)) continue;
+        bool nz = d != 0 && d != (1u << c);                // d == 2^c becomes digit 0 with a carry
         uint32_t neg = carry;
-        uint32_t mag = neg ? (1u << c) - d : d;  // 1 .. half
-        keys[pos] = fold_n ? mag - 1 : (uint32_t)w * half + (mag - 1);
-        vals[pos] = (fold_n ? (uint32_t)w * fold_n + i : i) | (neg << 31);
-        pos++;
+        uint32_t mag = neg ? (1u << c) - d : d;            // 1 .. half when nz
+        uint32_t key = fold_n ? mag - 1 : (uint32_t)w * half + (mag - 1);
+        uint32_t val = (fold_n ? (uint32_t)w * fold_n + i : i) | (neg << 31);
+        if (AGG) {
+            uint32_t grp = __match_any_sync(0xffffffffu, nz ? key : 0xffffffffu);
+            if (!nz) continue;
+            uint32_t leader = __ffs(grp) - 1, cnt = __popc(grp), rank = __popc(grp & ((1u << lane) - 1));
+            uint32_t base = 0;
+            if (lane == leader) base = atomicAdd(&count[key], cnt);
+            if (SCATTER) {
+                base = __shfl_sync(grp, base, leader);
+                vals[start[key] + base + rank] = val;
+            }
+        } else {
+            if (!nz) continue;
+            uint32_t base = atomicAdd(&count[key], 1u);
+            if (SCATTER) vals[start[key] + base] = val;
+        }
     }
 }
 
@@ -174,33 +196,42 @@ msm_window_table_kernel(const typename C::aff* __restrict__ bases, uint32_t n, i
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// bucket bounds and tasks
+// tasks
 // ---------------------------------------------------------------------------------------------------------
-static __global__ void msm_bounds_kernel(const uint32_t* __restrict__ keys, uint32_t m, uint32_t* __restrict__ start,
-                                  uint32_t* __restrict__ end) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    uint32_t k = keys[i];
-    if (i == 0 || keys[i - 1] != k) start[k] = i;
-    if (i == m - 1 || keys[i + 1] != k) end[k] = i + 1;
+constexpr uint32_t MSM_T_MAX = 512;
+constexpr uint32_t COMBINE_GROUP = 1024;
+constexpr uint32_t COMBINE_SMALL = 16;  // cut buckets with at most this many partial sums are summed by one thread
+
+// one thread: entry count -> task size.  Enough tasks to fill the machine several times over: a task is one thread's
+// dependency chain, so its length bounds the accumulation's tail; a cut bucket costs one extra full addition per task.
+static __global__ void msm_plan_kernel(const uint32_t* __restrict__ start, uint32_t nb, uint32_t slots, uint32_t t_min,
+                                       uint32_t t_fixed, MsmParams* __restrict__ prm) {
+    uint32_t m = start[nb];
+    uint32_t T = t_fixed;
+    if (T == 0) {
+        uint32_t t = m / slots;
+        T = t < t_min ? t_min : t > MSM_T_MAX ? MSM_T_MAX : t;
+    }
+    if (T < t_min) T = t_min;
+    prm->m = m;
+    prm->T = T;
+    prm->ncut = 0;
 }
 
 // per bucket: number of tasks, number of partial-sum slots (0 unless the bucket is cut), number of first-level
 // combine blocks (COMBINE_GROUP partial sums each), list of cut buckets
-constexpr uint32_t COMBINE_GROUP = 1024;
-constexpr uint32_t COMBINE_SMALL = 16;  // cut buckets with at most this many partial sums are summed by one thread
-static __global__ void msm_count_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end, uint32_t nb,
-                                       uint32_t T, uint32_t* __restrict__ ntasks, uint32_t* __restrict__ nparts,
-                                       uint32_t* __restrict__ nblk, uint32_t* __restrict__ cut_list,
-                                       uint32_t* __restrict__ cut_count) {
+static __global__ void msm_count_tasks_kernel(const uint32_t* __restrict__ start, uint32_t nb, MsmParams* __restrict__ prm,
+                                              uint32_t* __restrict__ ntasks, uint32_t* __restrict__ nparts,
+                                              uint32_t* __restrict__ nblk, uint32_t* __restrict__ cut_list) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k > nb) return;
+    const uint32_t T = prm->T;
     uint32_t t = 0;
-    if (k < nb) t = (end[k] - start[k] + T - 1) / T;
+    if (k < nb) t = (start[k + 1] - start[k] + T - 1) / T;
     ntasks[k] = t;
     nparts[k] = t > 1 ? t : 0;
     nblk[k] = t > COMBINE_SMALL ? (t + COMBINE_GROUP - 1) / COMBINE_GROUP : 0;
-    if (t > 1) cut_list[atomicAdd(cut_count, 1u)] = k;
+    if (t > 1) cut_list[atomicAdd(&prm->ncut, 1u)] = k;
 }
 
 // last k with base[k] <= j (base has nb+1 non-decreasing entries, base[nb] = total)
@@ -214,24 +245,80 @@ static __device__ __forceinline__ uint32_t msm_owner(const uint32_t* __restrict_
     return lo;
 }
 
-// task j -> (first entry, length, output slot); slot bit 31 set = partial-sum array, else bucket array
-static __global__ void msm_make_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ end,
-                                      const uint32_t* __restrict__ task_base, const uint32_t* __restrict__ part_base,
-                                      uint32_t nb, uint32_t nt, uint32_t T, uint32_t* __restrict__ t_begin,
-                                      uint32_t* __restrict__ t_len, uint32_t* __restrict__ t_out,
-                                      uint32_t* __restrict__ sort_key, uint32_t* __restrict__ sort_val) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= nt) return;
-    uint32_t k = msm_owner(task_base, nb, j);
-    uint32_t local = j - task_base[k];
-    uint32_t b = start[k] + local * T;
-    uint32_t len = min(T, end[k] - b);
-    uint32_t nt_k = task_base[k + 1] - task_base[k];
-    t_begin[j] = b;
-    t_len[j] = len;
-    t_out[j] = nt_k > 1 ? (0x80000000u | (part_base[k] + local)) : k;
-    sort_key[j] = T - len;  // longest tasks first
-    sort_val[j] = j;
+// task j -> (first entry, length, output slot); slot bit 31 set = partial-sum array, else bucket array.
+// Also the histogram of task lengths (shared-memory histogram per CTA, one global atomic per non-empty bin).
+static __global__ void __launch_bounds__(256)
+msm_make_tasks_kernel(const uint32_t* __restrict__ start, const uint32_t* __restrict__ task_base,
+                      const uint32_t* __restrict__ part_base, const uint32_t* __restrict__ blk_base, uint32_t nb,
+                      MsmParams* __restrict__ prm, uint32_t* __restrict__ t_begin, uint32_t* __restrict__ t_len,
+                      uint32_t* __restrict__ t_out, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t sh[MSM_T_MAX + 1];
+    for (uint32_t b = threadIdx.x; b <= MSM_T_MAX; b += blockDim.x) sh[b] = 0;
+    __syncthreads();
+    const uint32_t nt = task_base[nb], T = prm->T;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        prm->nt = nt;
+        prm->np = part_base[nb];
+        prm->nblk = blk_base[nb];
+    }
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < nt; j += gridDim.x * blockDim.x) {
+        uint32_t k = msm_owner(task_base, nb, j);
+        uint32_t local = j - task_base[k];
+        uint32_t b = start[k] + local * T;
+        uint32_t len = min(T, start[k + 1] - b);
+        uint32_t nt_k = task_base[k + 1] - task_base[k];
+        t_begin[j] = b;
+        t_len[j] = len;
+        t_out[j] = nt_k > 1 ? (0x80000000u | (part_base[k] + local)) : k;
+        atomicAdd(&sh[len], 1u);
+    }
+    __syncthreads();
+    for (uint32_t b = threadIdx.x; b <= MSM_T_MAX; b += blockDim.x)
+        if (sh[b]) atomicAdd(&hist[b], sh[b]);
+}
+
+// one CTA: cursor[len] = number of tasks longer than len (longest tasks first)
+static __global__ void __launch_bounds__(1024) msm_order_base_kernel(const uint32_t* __restrict__ hist, uint32_t* __restrict__ cursor) {
+    __shared__ uint32_t sh[1024];
+    uint32_t t = threadIdx.x;                       // bin of length MSM_T_MAX - t
+    uint32_t v = t <= MSM_T_MAX ? hist[MSM_T_MAX - t] : 0;
+    sh[t] = v;
+    __syncthreads();
+    for (uint32_t o = 1; o < 1024; o <<= 1) {
+        uint32_t a = t >= o ? sh[t - o] : 0;
+        __syncthreads();
+        sh[t] += a;
+        __syncthreads();
+    }
+    if (t <= MSM_T_MAX) cursor[MSM_T_MAX - t] = sh[t] - v;
+}
+
+// order[position] = task, positions by decreasing length: per tile of 1024 tasks a CTA ranks its tasks per length in
+// shared memory, reserves one range per length with a single global atomic, and writes
+static __global__ void __launch_bounds__(256)
+msm_order_tasks_kernel(const uint32_t* __restrict__ t_len, const MsmParams* __restrict__ prm, uint32_t* __restrict__ cursor,
+                       uint32_t* __restrict__ order) {
+    __shared__ uint32_t cnt[MSM_T_MAX + 1], base[MSM_T_MAX + 1];
+    const uint32_t nt = prm->nt;
+    for (uint32_t tile = blockIdx.x * 1024; tile < nt; tile += gridDim.x * 1024) {
+        for (uint32_t b = threadIdx.x; b <= MSM_T_MAX; b += blockDim.x) cnt[b] = 0;
+        __syncthreads();
+        uint32_t len[4], rank[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            uint32_t j = tile + q * 256 + threadIdx.x;
+            len[q] = j < nt ? t_len[j] : 0;
+            rank[q] = len[q] ? atomicAdd(&cnt[len[q]], 1u) : 0;
+        }
+        __syncthreads();
+        for (uint32_t b = threadIdx.x; b <= MSM_T_MAX; b += blockDim.x)
+            if (cnt[b]) base[b] = atomicAdd(&cursor[b], cnt[b]);
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+            if (len[q]) order[base[len[q]] + rank[q]] = tile + q * 256 + threadIdx.x;
+        __syncthreads();
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -240,33 +327,29 @@ static __global__ void msm_make_tasks_kernel(const uint32_t* __restrict__ start,
 // MINB = minimum resident CTAs per SM the register allocation must allow (G1: 144 registers give 3; 4 caps them at 128)
 template <class C, int MINB>
 __global__ void __launch_bounds__(128, MINB)
-msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const typename C::aff* __restrict__ merged,
-                      const uint32_t* __restrict__ vals, const uint32_t* __restrict__ order,
-                      const uint32_t* __restrict__ t_begin, const uint32_t* __restrict__ t_len,
-                      const uint32_t* __restrict__ t_out, uint32_t nt, typename C::pt* __restrict__ buckets,
+msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t* __restrict__ vals,
+                      const uint32_t* __restrict__ order, const uint32_t* __restrict__ t_begin,
+                      const uint32_t* __restrict__ t_len, const uint32_t* __restrict__ t_out,
+                      const MsmParams* __restrict__ prm, typename C::pt* __restrict__ buckets,
                       typename C::pt* __restrict__ parts) {
     typedef typename C::aff aff;
     typedef typename C::pt pt;
     uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= nt) return;
+    if (tid >= prm->nt) return;
     uint32_t j = order[tid];
     uint32_t e = t_begin[j], len = t_len[j], out = t_out[j];
     pt acc = C::identity();
-    // an entry is a base index (bit 31 = negate) or, after the pair merge, MSM_MERGED_FLAG | index of a merged point
-    auto fetch = [&](uint32_t v) -> aff {
-        return (v & MSM_MERGED_FLAG) ? merged[v & MSM_INDEX_MASK] : bases[v & MSM_INDEX_MASK];
-    };
     uint32_t v = vals[e];
-    aff q = fetch(v);
+    aff q = bases[v & MSM_INDEX_MASK];
     for (uint32_t k = 0; k < len; k++) {
         uint32_t vn = 0;
         aff qn = q;
         if (k + 1 < len) {  // prefetch the next point while this one is added
             vn = vals[e + k + 1];
-            qn = fetch(vn);
+            qn = bases[vn & MSM_INDEX_MASK];
         }
         if (v >> 31) q.y = C::field::neg(q.y);
-        if (!((v & MSM_MERGED_FLAG) && C::is_inf(q))) C::madd(acc, q);   // a merged pair of opposite points is infinity
+        C::madd(acc, q);
         v = vn;
         q = qn;
     }
@@ -274,163 +357,21 @@ msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const typename 
     else buckets[out] = acc;
 }
 
-// ---------------------------------------------------------------------------------------------------------
-// pair merge: one round of batched-affine addition in front of the accumulation
-// ---------------------------------------------------------------------------------------------------------
-// Sorted entries that share a bucket and sit on absolute positions (2g, 2g+1) are added in AFFINE coordinates:
-// (x3, y3) = (L^2 - x1 - x2, L (x1 - x3) - y1), L = (y2 - y1) / (x2 - x1), with the inversions batched by Montgomery's
-// trick over the P <= 256 pair slots of a thread (one Fermat inversion per thread).  That is 1 (prefix product) + 384/P
-// (inversion) + 2 (unwinding) + 3 (L, L^2, y3) = about 7.5 field products per addition against 10 for the XYZZ mixed
-// addition, on half of all additions.  The merged points go to `merged`, the entry list is rewritten compacted per
-// bucket (an entry is a base index | sign, or MERGED_FLAG | merged index), and the accumulation runs on the shorter
-// lists.  A bucket that starts on an odd position keeps its first entry single; so does one that ends on an even one.
-// output position of input position p of a bucket that starts at s
-static __device__ __forceinline__ uint32_t msm_merged_pos(uint32_t s, uint32_t p) { return s + ((p - s + (s & 1u)) >> 1); }
-
-static __global__ void msm_merged_end_kernel(const uint32_t* __restrict__ start, uint32_t* __restrict__ end, uint32_t nb) {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= nb) return;
-    uint32_t s = start[k], e = end[k];
-    if (e > s) end[k] = msm_merged_pos(s, e - 1) + 1;
-}
-
-// kind of a pair: 0 = generic (d = x2 - x1), 1 = doubling (d = 2 y1), 2 = opposite points (sum = infinity, d = 1)
-template <class C>
-static __device__ __forceinline__ int msm_pair_den(const typename C::aff& a, const typename C::aff& b, typename C::fe& d) {
-    typedef typename C::field F;
-    d = F::sub(b.x, a.x);
-    if (!F::is_zero(d)) return 0;
-    if (F::eq(a.y, b.y)) {
-        d = F::dbl(a.y);
-        return 1;
-    }
-    d = F::one();
-    return 2;
-}
-
-// one pair slot as loaded from memory (the loads of slot j+1 are issued before the arithmetic of slot j)
-template <class C>
-struct MsmPairSlot {
-    typename C::aff a, b;
-    uint32_t k0, v0, v1;
-    bool live, pair;   // live: g < nslots; pair: both positions exist and share a bucket
-};
-
-template <class C>
-static __device__ __forceinline__ MsmPairSlot<C> msm_pair_fetch(const typename C::aff* __restrict__ bases,
-                                                                const uint32_t* __restrict__ keys,
-                                                                const uint32_t* __restrict__ vals, uint32_t m,
-                                                                uint32_t nslots, uint32_t g) {
-    MsmPairSlot<C> s;
-    s.live = g < nslots;
-    s.pair = false;
-    if (!s.live) return s;
-    uint32_t p0 = 2 * g, p1 = p0 + 1;
-    s.k0 = keys[p0];
-    s.v0 = vals[p0];
-    s.v1 = 0;
-    if (p1 < m) {
-        s.v1 = vals[p1];
-        s.pair = keys[p1] == s.k0;
-    }
-    if (s.pair) {
-        s.a = bases[s.v0 & MSM_INDEX_MASK];
-        s.b = bases[s.v1 & MSM_INDEX_MASK];
-        if (s.v0 >> 31) s.a.y = C::field::neg(s.a.y);
-        if (s.v1 >> 31) s.b.y = C::field::neg(s.b.y);
-    }
-    return s;
-}
-
-// Thread t owns the slots t, t + T, t + 2T, ... (coalesced across a warp); the batch of one inversion is a thread's
-// per_thread slots.  It has to be large: the Fermat chain is 384 sequential products PER LANE, so it is amortised
-// only over the slots of that lane (a warp-wide batch with one shared inversion was measured 3x slower: the
-// inversion's instruction stream costs a warp the same whether one lane or thirty-two use its result).
-template <class C>
-__global__ void __launch_bounds__(128)
-msm_pair_merge_kernel(const typename C::aff* __restrict__ bases, const uint32_t* __restrict__ keys,
-                      const uint32_t* __restrict__ vals, const uint32_t* __restrict__ start, uint32_t m, uint32_t nslots,
-                      uint32_t per_thread, typename C::fe* __restrict__ prefix, typename C::aff* __restrict__ merged,
-                      uint32_t* __restrict__ vals_out) {
-    typedef typename C::field F;
-    typedef typename C::fe fe;
-    typedef typename C::aff aff;
-    typedef MsmPairSlot<C> slot_t;
-    const uint32_t T = gridDim.x * blockDim.x;
-    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    // forward: prefix products of the denominators of this thread's slots
-    fe prod = F::one();
-    {
-        slot_t cur = msm_pair_fetch<C>(bases, keys, vals, m, nslots, t);
-        for (uint32_t j = 0; j < per_thread; j++) {
-            uint32_t g = t + j * T;
-            slot_t nxt = msm_pair_fetch<C>(bases, keys, vals, m, nslots, j + 1 < per_thread ? g + T : nslots);
-            if (cur.pair) {
-                fe d;
-                msm_pair_den<C>(cur.a, cur.b, d);
-                prefix[g] = prod;
-                prod = F::mul(prod, d);
-            }
-            cur = nxt;
-        }
-    }
-    fe inv = F::inv(prod);
-    // backward: unwind the inverses, finish the additions, rewrite the entries
-    uint32_t jl = per_thread - 1;
-    slot_t cur = msm_pair_fetch<C>(bases, keys, vals, m, nslots, t + jl * T);
-    fe pre = cur.pair ? prefix[t + jl * T] : F::one();
-    for (uint32_t j = per_thread; j-- > 0;) {
-        uint32_t g = t + j * T;
-        slot_t nxt = msm_pair_fetch<C>(bases, keys, vals, m, nslots, j > 0 ? g - T : nslots);
-        fe npre = nxt.pair ? prefix[g - T] : F::one();
-        if (cur.live) {
-            uint32_t p0 = 2 * g, p1 = p0 + 1;
-            if (!cur.pair) {
-                // two singles: the last entry of one bucket, the first of the next (or the odd entry that ends the list)
-                vals_out[msm_merged_pos(start[cur.k0], p0)] = cur.v0;
-                if (p1 < m) vals_out[p1] = cur.v1;   // start of its bucket: position unchanged
-            } else {
-                fe d;
-                int kind = msm_pair_den<C>(cur.a, cur.b, d);
-                fe dinv = F::mul(inv, pre);
-                inv = F::mul(inv, d);
-                aff r;
-                if (kind == 2) {
-                    r.x = F::zero();
-                    r.y = F::zero();   // infinity: the accumulation skips it
-                } else {
-                    fe num;
-                    if (kind == 0) num = F::sub(cur.b.y, cur.a.y);
-                    else {
-                        fe xx = F::sqr(cur.a.x);
-                        num = F::add(F::dbl(xx), xx);
-                    }
-                    fe lam = F::mul(num, dinv);
-                    r.x = F::sub(F::sub(F::sqr(lam), cur.a.x), cur.b.x);
-                    r.y = F::sub(F::mul(lam, F::sub(cur.a.x, r.x)), cur.a.y);
-                }
-                merged[g] = r;
-                vals_out[msm_merged_pos(start[cur.k0], p0)] = MSM_MERGED_FLAG | g;
-            }
-        }
-        cur = nxt;
-        pre = npre;
-    }
-}
-
 // Most cut buckets hold a handful of partial sums (a bucket a few times over the task size): one thread each.
 template <class C>
 __global__ void __launch_bounds__(128)
-msm_combine_small_kernel(const uint32_t* __restrict__ cut_list, uint32_t ncut, const uint32_t* __restrict__ part_base,
-                         const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ buckets) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= ncut) return;
-    uint32_t k = cut_list[i];
-    uint32_t b = part_base[k], e = part_base[k + 1];
-    if (e - b > COMBINE_SMALL) return;
-    typename C::pt acc = parts[b];
-    for (uint32_t j = b + 1; j < e; j++) C::add(acc, parts[j]);
-    buckets[k] = acc;
+msm_combine_small_kernel(const uint32_t* __restrict__ cut_list, const MsmParams* __restrict__ prm,
+                         const uint32_t* __restrict__ part_base, const typename C::pt* __restrict__ parts,
+                         typename C::pt* __restrict__ buckets) {
+    const uint32_t ncut = prm->ncut;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < ncut; i += gridDim.x * blockDim.x) {
+        uint32_t k = cut_list[i];
+        uint32_t b = part_base[k], e = part_base[k + 1];
+        if (e - b > COMBINE_SMALL) continue;
+        typename C::pt acc = parts[b];
+        for (uint32_t j = b + 1; j < e; j++) C::add(acc, parts[j]);
+        buckets[k] = acc;
+    }
 }
 
 // The heavy cut buckets are summed in two levels so that a bucket holding a quarter of all points (the digit-1 bucket of a
@@ -439,28 +380,36 @@ msm_combine_small_kernel(const uint32_t* __restrict__ cut_list, uint32_t ncut, c
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 msm_combine1_kernel(const uint32_t* __restrict__ blk_base, const uint32_t* __restrict__ part_base, uint32_t nb,
-                    const typename C::pt* __restrict__ parts, typename C::pt* __restrict__ parts2) {
-    uint32_t k = msm_owner(blk_base, nb, blockIdx.x);
-    uint32_t g = blockIdx.x - blk_base[k];
-    uint32_t b = part_base[k] + g * COMBINE_GROUP;
-    uint32_t e = min(part_base[k + 1], b + COMBINE_GROUP);
-    typename C::pt acc = C::identity();
-    for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts[i]);
-    block_sum_points<C, THREADS>(acc);
-    if (threadIdx.x == 0) parts2[blockIdx.x] = acc;
+                    const MsmParams* __restrict__ prm, const typename C::pt* __restrict__ parts,
+                    typename C::pt* __restrict__ parts2) {
+    const uint32_t nblk = prm->nblk;
+    for (uint32_t blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+        uint32_t k = msm_owner(blk_base, nb, blk);
+        uint32_t g = blk - blk_base[k];
+        uint32_t b = part_base[k] + g * COMBINE_GROUP;
+        uint32_t e = min(part_base[k + 1], b + COMBINE_GROUP);
+        typename C::pt acc = C::identity();
+        for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts[i]);
+        block_sum_points<C, THREADS>(acc);
+        if (threadIdx.x == 0) parts2[blk] = acc;
+    }
 }
 
 template <class C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
 msm_combine2_kernel(const uint32_t* __restrict__ cut_list, const uint32_t* __restrict__ blk_base,
-                    const typename C::pt* __restrict__ parts2, typename C::pt* __restrict__ buckets) {
-    uint32_t k = cut_list[blockIdx.x];
-    uint32_t b = blk_base[k], e = blk_base[k + 1];
-    typename C::pt acc = C::identity();
-    if (e == b) return;  // a small cut bucket: msm_combine_small_kernel wrote it
-    for (uint32_t i = b + threadIdx.x; i < e; i += THREADS) C::add(acc, parts2[i]);
-    block_sum_points<C, THREADS>(acc);
-    if (threadIdx.x == 0) buckets[k] = acc;
+                    const MsmParams* __restrict__ prm, const typename C::pt* __restrict__ parts2,
+                    typename C::pt* __restrict__ buckets) {
+    const uint32_t ncut = prm->ncut;
+    for (uint32_t i = blockIdx.x; i < ncut; i += gridDim.x) {
+        uint32_t k = cut_list[i];
+        uint32_t b = blk_base[k], e = blk_base[k + 1];
+        if (e == b) continue;  // a small cut bucket: msm_combine_small_kernel wrote it (uniform over the CTA)
+        typename C::pt acc = C::identity();
+        for (uint32_t j = b + threadIdx.x; j < e; j += THREADS) C::add(acc, parts2[j]);
+        block_sum_points<C, THREADS>(acc);
+        if (threadIdx.x == 0) buckets[k] = acc;
+    }
 }
 
 // Bucket reduction, sum_b (b+1) B_b per window, in two levels so that no thread multiplies by its chunk offset at
@@ -585,7 +534,7 @@ __global__ void msm_inf_mask_kernel(const typename C::aff* __restrict__ bases, u
 
 
 // ---------------------------------------------------------------------------------------------------------
-// host side: workspace + staged launch
+// host side: workspace + enqueue
 // ---------------------------------------------------------------------------------------------------------
 // Witness-scalar MSMs (A, B1, B2, C): most scalars are 0/1 or below 2^64, so there is about one non-zero digit per
 // point instead of W; narrower windows keep the bucket reduction (2 full additions per bucket per window) in
@@ -604,13 +553,20 @@ static inline int msm_pick_c_table(size_t n) {
     while (c > 6 && msm_num_windows(c - 1) == W) c--;
     return c;
 }
+// the same for witness-like scalars: 2 bits narrower than the dense choice (a third of the entries of a dense MSM,
+// so the one bucket set must be smaller for its reduction to stay in proportion)
+static inline int msm_pick_c_table_sparse(size_t n) {
+    int c = msm_pick_c(n) + 2;
+    if (c > 22) c = 22;
+    return c;
+}
 
 struct MsmConfig {
     bool sparse = false;  // scalars are witness-like (see msm_pick_c_sparse)
     int c = 0;          // window bits (0 = pick from n)
     uint32_t T = 0;     // max entries per task (0 = from the entry count: about 1024 tasks' worth of work per SM)
     uint32_t L = 0;     // buckets per reduction chunk (0 = from the bucket count)
-    bool table = false; // fixed-base window table (build_table() before the first run); dense scalars only
+    bool table = false; // fixed-base window table (build_table() before the first run)
 };
 
 // Counters a finished MSM leaves behind (for bench.py's work model and tests)
@@ -631,12 +587,10 @@ public:
 
     Msm() {}
     ~Msm() {
-        if (h_counters) cudaFreeHost(h_counters);
+        if (h_params) cudaFreeHost(h_params);
         if (h_windows) cudaFreeHost(h_windows);
         if (ev_acc0) cudaEventDestroy(ev_acc0);
         if (ev_acc1) cudaEventDestroy(ev_acc1);
-        if (ev_mrg0) cudaEventDestroy(ev_mrg0);
-        if (ev_mrg1) cudaEventDestroy(ev_mrg1);
         for (auto& e : ev_t)
             if (e) cudaEventDestroy(e);
     }
@@ -650,48 +604,51 @@ public:
     static size_t table_bytes(size_t n, int c) { return size_t(msm_num_windows(c)) * n * sizeof(aff); }
 
     // timeline of the last run relative to `base` (an event recorded earlier), milliseconds:
-    // [0] start, [1] digits done, [2] sort + task counts done, [3] accumulate starts, [4] accumulate done, [5] window sums on the host
+    // [0] start, [1] digits counted, [2] entries scattered + tasks ordered, [3] accumulate starts, [4] accumulate done,
+    // [5] window sums on the host
     void trace(cudaEvent_t base, float out[6]) const {
         cudaEvent_t e[6] = {ev_t[0], ev_t[1], ev_t[2], ev_acc0, ev_acc1, ev_t[3]};
         for (int i = 0; i < 6; i++) {
             out[i] = -1;
-            if ((i == 3 || i == 4) && !acc_timed) continue;
+            if (!enqueued) continue;
             float ms = 0;
             if (cudaEventElapsedTime(&ms, base, e[i]) == cudaSuccess) out[i] = ms;
         }
     }
 
-    // duration of the last accumulate kernel (CUDA events on its own stream); valid once the stream is synchronised
+    // duration of the last accumulate kernel (CUDA events on its own stream); valid once wait() returned
     float accumulate_ms() const {
-        float ms = 0, mg = 0;
-        if (!acc_timed || cudaEventElapsedTime(&ms, ev_acc0, ev_acc1) != cudaSuccess) return 0;
-        if (merged_slots && cudaEventElapsedTime(&mg, ev_mrg0, ev_mrg1) == cudaSuccess) ms += mg;  // the pair merge is part of it
+        float ms = 0;
+        if (!enqueued || cudaEventElapsedTime(&ms, ev_acc0, ev_acc1) != cudaSuccess) return 0;
         return ms;
     }
 
-    // stage 1: digits (async).  scalars/bases/mask are device pointers; n <= reserved capacity.
-    void stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s);
+    // Enqueue the whole MSM; nothing here waits for the device.  Counting sort of the digits and the task list go on
+    // `s`; the accumulation and the reductions on `s_acc` (nullptr = the same stream): the prover keeps the H MSM's
+    // preparation on the high-priority transform stream and its accumulation on the lowest-priority one, so that it
+    // fills the machine under everything else.  scalars/bases/mask are device pointers; n <= reserved capacity.
+    void enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s,
+                 cudaStream_t s_acc = nullptr);
 
-    // stage 2: sort + task counts (reads the entry count -> one stream sync)
-    void stage2();
-
-    // stage 3: accumulate + reductions (reads the task count -> one stream sync); window sums go to the host.
-    // `s3` (optional) = a different stream for this stage: the prover keeps the H MSM's digits + sort on the
-    // high-priority transform stream (so the sort is not starved by the witness MSMs' accumulations) and its
-    // accumulation on the lowest-priority stream (so it fills the machine under everything else).
-    void stage3(cudaStream_t s3 = nullptr);
+    // block until the window sums and counters of the last enqueue() are in host memory
+    void wait() {
+        if (!enqueued) return;
+        G16_CUDA(cudaEventSynchronize(ev_t[3]));
+        stats = MsmStats();
+        stats.entries = h_params->m; stats.c = c; stats.W = Wd; stats.buckets = nb; stats.T = h_params->T;
+        stats.tasks = h_params->nt;
+        stats.cut_buckets = h_params->ncut;
+    }
 
     // whole MSM on one stream; returns after the window sums are in host memory
     void run(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
-        stage1(bases_, scalars, inf_mask, n_, s);
-        stage2();
-        stage3();
-        G16_CUDA(cudaStreamSynchronize(s));
+        enqueue(bases_, scalars, inf_mask, n_, s);
+        wait();
     }
 
     // sum_w 2^(c w) S_w on the host (255 dependent doublings: a latency chain, an order of magnitude quicker on a
     // CPU core than on one GPU thread).  HC = g16h::HG1 / HG2, whose XYZZ layout equals the device one.
-    // Valid after the stream is synchronised.
+    // Valid after wait().
     template <class HC>
     typename HC::pt finish() const {
         static_assert(sizeof(typename HC::pt) == sizeof(pt), "host/device point layouts differ");
@@ -708,20 +665,12 @@ public:
     MsmStats stats;
     int c = 0, W = 0;    // W = windows of the bucket problem (1 with a table)
     int Wd = 0;          // digit windows = rows of the table
-    uint32_t T = 0, L = 0, L1 = 4;
+    uint32_t L = 0, L1 = 4;
 
 private:
     static int acc_minb() {   // 4 = the 128-register build of the G1 accumulation (4 CTAs/SM; measured 1-2 % faster than
                               // the 148-register one); G16_ACC_MINB=1 selects the other for comparison
         static int v = [] { const char* e = std::getenv("G16_ACC_MINB"); return e ? std::atoi(e) : 4; }();
-        return v;
-    }
-    static bool merge_enabled() {   // G16_PAIR_MERGE=1: batched-affine pair round in front of the accumulation
-        static bool v = [] { const char* e = std::getenv("G16_PAIR_MERGE"); return e && std::atoi(e) != 0; }();
-        return v;
-    }
-    static size_t merge_min() {     // fewest entries for which the pair round pays (G16_PAIR_MERGE_MIN overrides; tests use 0)
-        static size_t v = [] { const char* e = std::getenv("G16_PAIR_MERGE_MIN"); return e ? size_t(std::atoll(e)) : size_t(1) << 20; }();
         return v;
     }
     static constexpr int RED_THREADS = 128;
@@ -732,31 +681,20 @@ private:
         uint32_t k = per_window / 512;
         return k < 32 ? 32 : k > 256 ? 256 : k;
     }
-    static void grow(DevBuf& b, size_t bytes) {
-        if (bytes > b.bytes) b.alloc(bytes + bytes / 4 + 4096);
-    }
-    int key_bits() const {
-        int b = 1;
-        while ((size_t(1) << b) < nb) b++;
-        return b;
-    }
     MsmConfig cfg;
-    size_t cap_n = 0, n = 0, m = 0, slots = 148 * 1024;
+    size_t cap_n = 0, n = 0, slots = 148 * 1024;
+    int sms = 148;
     uint32_t bpw = 0, nb = 0, cpw = 0, cpw1 = 0, ns0 = 0, ns1 = 0;
+    uint32_t nt_max = 0, np_max = 0, nblk_max = 0, ncut_max = 0;
     const aff* bases = nullptr;
-    cudaStream_t stream = 0;
-    uint32_t *sorted_keys = nullptr, *sorted_vals = nullptr;
-    DevBuf keys_a, keys_b, vals_a, vals_b, start, end, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
-        t_begin, t_len, t_out, tk_a, tk_b, tv_a, tv_b, buckets, parts, parts2, merged, prefix, chunk_out, chunk_sum, chunk2_out, slice_out, slice1_out,
-        window_out, counters, cub_tmp,
-        task_tmp, table;
+    DevBuf vals, count, start, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
+        t_begin, t_len, t_out, order, hist, buckets, parts, parts2, chunk_out, chunk_sum, chunk2_out, slice_out,
+        slice1_out, window_out, params, cub_tmp, table;
     size_t table_n = 0;
-    unsigned long long* h_counters = nullptr;
+    MsmParams* h_params = nullptr;
     pt* h_windows = nullptr;
-    cudaEvent_t ev_mrg0 = nullptr, ev_mrg1 = nullptr;
-    uint32_t merged_slots = 0;
     cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr, ev_t[4] = {nullptr, nullptr, nullptr, nullptr};
-    bool acc_timed = false;
+    bool enqueued = false;
 };
 
 #ifdef G16_MSM_INSTANTIATE
@@ -765,32 +703,52 @@ template <class C>
 void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     cfg = cfg_in;
     cap_n = n;
-    c = cfg.c ? cfg.c : cfg.table ? msm_pick_c_table(n) : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
+    c = cfg.c ? cfg.c
+        : cfg.table ? (cfg.sparse ? msm_pick_c_table_sparse(n) : msm_pick_c_table(n))
+        : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
     if (c < 2) c = 2;
     if (c > 24) c = 24;
     if (cfg.table && c < 6) c = 6;
     Wd = msm_num_windows(c);
     W = cfg.table ? 1 : Wd;
+    if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
     bpw = 1u << (c - 1);
     nb = uint32_t(W) * bpw;
     size_t m_max = n * size_t(Wd);
+    // entry positions and counters are 32-bit; cub's scans take int item counts (nb + 1 <= 2^31 always holds here)
     if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
-    if (cfg.table && m_max > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM window table too large for 30-bit base indices; shard it");
+    if (cfg.table && m_max > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM window table too large for 31-bit base indices; shard it");
+    if (n > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM too large for 31-bit base indices; shard it");
+    if (cfg.T > T_MAX) cfg.T = T_MAX;
     // level-0 chunks: 16 buckets when there are enough buckets to fill the machine with chunk threads, else 8
     // (half the dependency chain); level 1 works on bpw/L points only, so its chunks are short (latency, not work)
     L = cfg.L ? cfg.L : (nb >= (2u << 20) ? 16 : 8);
     L1 = 4;
     cpw = (bpw + L - 1) / L;
-    int dev = 0, sms = 148;
+    int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     slots = size_t(sms) * (sizeof(pt) > 128 ? 512 : 1024);
+    // Bounds that hold for every scalar vector (msm_plan_kernel picks T = clamp(m / slots, T_MIN, T_MAX) on the
+    // device): q >= m / T, tasks <= non-empty buckets + q, partial sums <= 2 q (a cut bucket has more than T
+    // entries), combine blocks < partial sums / 16 (a bucket with blocks has more than COMBINE_SMALL partial sums)
+    size_t q = cfg.T ? m_max / (cfg.T < T_MIN ? T_MIN : cfg.T) + 1 : std::max(2 * slots + 2, m_max / T_MAX + 1);
+    if (q > m_max / T_MIN + 1) q = m_max / T_MIN + 1;
+    nt_max = uint32_t(std::min<size_t>(size_t(nb) + q, m_max ? m_max : 1));
+    np_max = uint32_t(std::min<size_t>(2 * q, m_max ? m_max : 1));
+    nblk_max = np_max / COMBINE_SMALL + 1;
+    ncut_max = uint32_t(std::min<size_t>(nb, q));
     size_t e = m_max ? m_max : 1;
-    keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_a.alloc(e * 4); vals_b.alloc(e * 4);
-    start.alloc(size_t(nb) * 4); end.alloc(size_t(nb) * 4);
+    vals.alloc(e * 4);
+    count.alloc(size_t(nb + 1) * 4); start.alloc(size_t(nb + 1) * 4);
     ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4); nblk.alloc(size_t(nb + 1) * 4);
     task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
-    cut_list.alloc((m_max / T_MIN + 2) * 4);  // a cut bucket holds more than T >= T_MIN entries
+    cut_list.alloc((size_t(ncut_max) + 1) * 4);
+    t_begin.alloc(size_t(nt_max) * 4); t_len.alloc(size_t(nt_max) * 4); t_out.alloc(size_t(nt_max) * 4);
+    order.alloc(size_t(nt_max) * 4);
+    hist.alloc(2 * (MSM_T_MAX + 1) * 4);   // length histogram, then the cursors
+    parts.alloc(size_t(np_max) * sizeof(pt));
+    parts2.alloc(size_t(nblk_max) * sizeof(pt));
     buckets.alloc(size_t(nb) * sizeof(pt));
     cpw1 = (cpw + L1 - 1) / L1;
     chunk_out.alloc(size_t(W) * cpw * sizeof(pt));
@@ -801,22 +759,17 @@ void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     slice_out.alloc(size_t(W) * (ns0 ? ns0 : 1) * sizeof(pt));
     slice1_out.alloc(size_t(W) * (ns1 ? ns1 : 1) * sizeof(pt));
     window_out.alloc(size_t(W) * sizeof(pt));
-    counters.alloc(64);
-    size_t t1 = 0, t3 = 0;
-    cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
-    cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
-    cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)e, 0, key_bits());
-    cub::DeviceScan::ExclusiveSum(nullptr, t3, ntasks.as<uint32_t>(), task_base.as<uint32_t>(), (int)(nb + 1));
-    cub_tmp.alloc((t1 > t3 ? t1 : t3) + 256);
-    if (!h_counters) G16_CUDA(cudaMallocHost(&h_counters, 64));
-    if (!h_windows) G16_CUDA(cudaMallocHost(&h_windows, 32 * sizeof(pt) * 8));
-    if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
+    params.alloc(sizeof(MsmParams));
+    size_t t3 = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, t3, count.as<uint32_t>(), start.as<uint32_t>(), (int)(nb + 1));
+    cub_tmp.alloc(t3 + 256);
+    if (!h_params) G16_CUDA(cudaMallocHost(&h_params, sizeof(MsmParams)));
+    if (!h_windows) G16_CUDA(cudaMallocHost(&h_windows, 256 * sizeof(pt)));
     if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
     if (!ev_acc1) G16_CUDA(cudaEventCreate(&ev_acc1));
-    if (!ev_mrg0) G16_CUDA(cudaEventCreate(&ev_mrg0));
-    if (!ev_mrg1) G16_CUDA(cudaEventCreate(&ev_mrg1));
     for (auto& e : ev_t)
         if (!e) G16_CUDA(cudaEventCreate(&e));
+    enqueued = false;
 }
 
 template <class C>
@@ -832,156 +785,87 @@ size_t Msm<C>::build_table(const aff* bases_, size_t n_, cudaStream_t s) {
 }
 
 template <class C>
-void Msm<C>::stage1(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s) {
+void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s,
+                     cudaStream_t s_acc) {
     if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
     if (cfg.table && n_ != table_n) throw std::runtime_error("MSM: window table was built for a different base count");
     bases = cfg.table && n_ ? table.template as<aff>() : bases_;
     n = n_;
-    stream = s;
+    uint32_t* cnt = count.as<uint32_t>();
+    uint32_t* st = start.as<uint32_t>();
+    MsmParams* prm = params.as<MsmParams>();
+    const uint32_t fold = cfg.table ? (uint32_t)n : 0u;
+    const unsigned dgrid = (unsigned)((n + 255) / 256);
+    // warp-aggregated counters unless the scalars are known to be dense and uniform (the H MSM over its window table)
+    const bool agg = !(cfg.table && !cfg.sparse);
     G16_CUDA(cudaEventRecord(ev_t[0], s));
-    G16_CUDA(cudaMemsetAsync(counters.p, 0, 64, s));
+    // ---- counting sort of the digits by bucket
+    G16_CUDA(cudaMemsetAsync(cnt, 0, size_t(nb + 1) * 4, s));
     if (n) {
-        msm_digits_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd,
-                                                                      cfg.table ? (uint32_t)n : 0u,
-                                                                      keys_a.as<uint32_t>(), vals_a.as<uint32_t>(),
-                                                                      counters.as<unsigned long long>());
-        G16_CUDA(cudaGetLastError());
+        if (agg) msm_digits_kernel<false, true><<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, fold, cnt, nullptr, nullptr);
+        else msm_digits_kernel<false, false><<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, fold, cnt, nullptr, nullptr);
         G16_LAUNCHED(1);
     }
-    acc_timed = false;
-    G16_CUDA(cudaEventRecord(ev_t[1], s));
-    G16_CUDA(cudaMemcpyAsync(h_counters, counters.p, 16, cudaMemcpyDeviceToHost, s));
-}
-
-template <class C>
-void Msm<C>::stage2() {
-    cudaStream_t s = stream;
-    G16_CUDA(cudaStreamSynchronize(s));
-    m = (size_t)h_counters[0];
-    T = cfg.T;
-    if (T == 0) {
-        // enough tasks to fill the machine several times over: a task is one thread's dependency chain, so its
-        // length bounds the kernel's tail; a cut bucket costs one extra full addition per task
-        size_t t = (merge_enabled() ? m / 2 : m) / slots;
-        T = uint32_t(t < T_MIN ? T_MIN : t > T_MAX ? T_MAX : t);
-    }
-    if (T < T_MIN) T = T_MIN;
-    stats = MsmStats();
-    stats.entries = m; stats.c = c; stats.W = Wd; stats.buckets = nb; stats.T = T;
-    G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
-    if (m == 0) {
-        G16_CUDA(cudaEventRecord(ev_t[2], s));
-        return;
-    }
-    cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
-    cub::DoubleBuffer<uint32_t> dv(vals_a.as<uint32_t>(), vals_b.as<uint32_t>());
     size_t tb = cub_tmp.bytes;
-    G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, dk, dv, (int)m, 0, key_bits(), s));
-    sorted_keys = dk.Current();
-    sorted_vals = dv.Current();
-    G16_CUDA(cudaMemsetAsync(start.p, 0, size_t(nb) * 4, s));
-    G16_CUDA(cudaMemsetAsync(end.p, 0, size_t(nb) * 4, s));
-    msm_bounds_kernel<<<(unsigned)((m + 255) / 256), 256, 0, s>>>(sorted_keys, (uint32_t)m, start.as<uint32_t>(),
-                                                                  end.as<uint32_t>());
-    merged_slots = 0;
-    if (merge_enabled() && m >= merge_min() && ((m + 1) / 2) * (sizeof(aff) + sizeof(fe)) <= (size_t(24) << 30)) {
-        // one round of batched-affine pair additions in front of the accumulation (see msm_pair_merge_kernel)
-        uint32_t nslots = uint32_t((m + 1) / 2);
-        grow(merged, size_t(nslots) * sizeof(aff));
-        grow(prefix, size_t(nslots) * sizeof(fe));
-        uint32_t want = uint32_t(slots / 2);                 // threads that fill the machine
-        uint32_t per = (nslots + want - 1) / want;
-        per = per < 32 ? 32 : per > 256 ? 256 : per;         // slots per thread = the inversion's batch
-        uint32_t blocks = ((nslots + per - 1) / per + 127) / 128;
-        per = (nslots + blocks * 128 - 1) / (blocks * 128);
-        G16_CUDA(cudaEventRecord(ev_mrg0, s));
-        msm_pair_merge_kernel<C><<<blocks, 128, 0, s>>>(bases, sorted_keys, sorted_vals, start.as<uint32_t>(), (uint32_t)m,
-                                                        nslots, per, prefix.as<fe>(), merged.as<aff>(), dv.Alternate());
-        G16_CUDA(cudaEventRecord(ev_mrg1, s));
-        msm_merged_end_kernel<<<(nb + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb);
-        G16_CUDA(cudaGetLastError());
-        G16_LAUNCHED(2);
-        sorted_vals = dv.Alternate();
-        merged_slots = nslots;
+    G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, cnt, st, (int)(nb + 1), s));
+    msm_plan_kernel<<<1, 1, 0, s>>>(st, nb, (uint32_t)slots, T_MIN, cfg.T, prm);
+    G16_CUDA(cudaEventRecord(ev_t[1], s));
+    G16_CUDA(cudaMemsetAsync(cnt, 0, size_t(nb + 1) * 4, s));
+    if (n) {
+        if (agg) msm_digits_kernel<true, true><<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, fold, cnt, st, vals.as<uint32_t>());
+        else msm_digits_kernel<true, false><<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, fold, cnt, st, vals.as<uint32_t>());
+        G16_LAUNCHED(1);
     }
-    uint32_t* cut_count = counters.as<uint32_t>() + 4;  // byte offset 16
-    msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(start.as<uint32_t>(), end.as<uint32_t>(), nb, T,
-                                                                ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
-                                                                nblk.as<uint32_t>(), cut_list.as<uint32_t>(), cut_count);
-    G16_LAUNCHED(2);
+    // ---- tasks, longest first
+    msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(st, nb, prm, ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
+                                                                nblk.as<uint32_t>(), cut_list.as<uint32_t>());
     uint32_t* src[3] = {ntasks.as<uint32_t>(), nparts.as<uint32_t>(), nblk.as<uint32_t>()};
     uint32_t* dst[3] = {task_base.as<uint32_t>(), part_base.as<uint32_t>(), blk_base.as<uint32_t>()};
-    uint32_t* h32 = reinterpret_cast<uint32_t*>(h_counters);
     for (int i = 0; i < 3; i++) {
         tb = cub_tmp.bytes;
         G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, src[i], dst[i], (int)(nb + 1), s));
-        // h32[4] = tasks, [5] = partial sums, [6] = combine blocks, [7] = cut buckets
-        G16_CUDA(cudaMemcpyAsync(h32 + 4 + i, dst[i] + nb, 4, cudaMemcpyDeviceToHost, s));
     }
-    G16_CUDA(cudaMemcpyAsync(h32 + 7, cut_count, 4, cudaMemcpyDeviceToHost, s));
+    uint32_t* hs = hist.as<uint32_t>();
+    uint32_t* cursor = hs + (MSM_T_MAX + 1);
+    G16_CUDA(cudaMemsetAsync(hs, 0, (MSM_T_MAX + 1) * 4, s));
+    const unsigned tgrid = (unsigned)std::min<size_t>((size_t(nt_max) + 255) / 256, size_t(sms) * 8);
+    msm_make_tasks_kernel<<<tgrid, 256, 0, s>>>(st, task_base.as<uint32_t>(), part_base.as<uint32_t>(), blk_base.as<uint32_t>(),
+                                                nb, prm, t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), hs);
+    msm_order_base_kernel<<<1, 1024, 0, s>>>(hs, cursor);
+    const unsigned ogrid = (unsigned)std::min<size_t>((size_t(nt_max) + 1023) / 1024, size_t(sms) * 8);
+    msm_order_tasks_kernel<<<ogrid, 256, 0, s>>>(t_len.as<uint32_t>(), prm, cursor, order.as<uint32_t>());
+    G16_CUDA(cudaGetLastError());
+    G16_LAUNCHED(5);
     G16_CUDA(cudaEventRecord(ev_t[2], s));
-}
-
-template <class C>
-void Msm<C>::stage3(cudaStream_t s3) {
-    cudaStream_t s = s3 ? s3 : stream;
-    if (s != stream) G16_CUDA(cudaStreamWaitEvent(s, ev_t[2], 0));
-    if (m != 0) {
-        G16_CUDA(cudaStreamSynchronize(stream));
-        const uint32_t* h32 = reinterpret_cast<const uint32_t*>(h_counters);
-        uint32_t nt = h32[4], np = h32[5], nblocks = h32[6], ncut = h32[7];
-        stats.tasks = nt;
-        stats.cut_buckets = ncut;
-        // the stream is idle here, so growing these is safe
-        grow(t_begin, size_t(nt) * 4); grow(t_len, size_t(nt) * 4); grow(t_out, size_t(nt) * 4);
-        grow(tk_a, size_t(nt) * 4); grow(tk_b, size_t(nt) * 4); grow(tv_a, size_t(nt) * 4); grow(tv_b, size_t(nt) * 4);
-        grow(parts, size_t(np) * sizeof(pt));
-        grow(parts2, size_t(nblocks) * sizeof(pt));
-        cub::DoubleBuffer<uint32_t> tk(tk_a.as<uint32_t>(), tk_b.as<uint32_t>());
-        cub::DoubleBuffer<uint32_t> tv(tv_a.as<uint32_t>(), tv_b.as<uint32_t>());
-        int bits = 1;
-        while ((1u << bits) <= T) bits++;
-        size_t need = 0;
-        cub::DeviceRadixSort::SortPairs(nullptr, need, tk, tv, (int)nt, 0, bits);
-        grow(task_tmp, need + 256);
-        msm_make_tasks_kernel<<<(nt + 255) / 256, 256, 0, s>>>(
-            start.as<uint32_t>(), end.as<uint32_t>(), task_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, nt, T,
-            t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), tk_a.as<uint32_t>(),
-            tv_a.as<uint32_t>());
-        size_t tb = task_tmp.bytes;
-        G16_CUDA(cub::DeviceRadixSort::SortPairs(task_tmp.p, tb, tk, tv, (int)nt, 0, bits, s));
-        G16_CUDA(cudaEventRecord(ev_acc0, s));
-        bool launched = false;
-        if constexpr (sizeof(pt) <= 128) {
-            if (acc_minb() == 4) {
-                msm_accumulate_kernel<C, 4><<<(nt + 127) / 128, 128, 0, s>>>(
-                    bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(),
-                    nt, buckets.as<pt>(), parts.as<pt>());
-                launched = true;
-            }
-        }
-        if (!launched)
-            msm_accumulate_kernel<C, 1><<<(nt + 127) / 128, 128, 0, s>>>(
-                bases, merged.as<aff>(), sorted_vals, tv.Current(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), nt,
-                buckets.as<pt>(), parts.as<pt>());
-        G16_CUDA(cudaEventRecord(ev_acc1, s));
-        acc_timed = true;
-        G16_CUDA(cudaGetLastError());
-        G16_LAUNCHED(2);
-        if (ncut) {
-            msm_combine_small_kernel<C><<<(ncut + 127) / 128, 128, 0, s>>>(
-                cut_list.as<uint32_t>(), ncut, part_base.as<uint32_t>(), parts.as<pt>(), buckets.as<pt>());
-            G16_LAUNCHED(1);
-            if (nblocks) {
-                msm_combine1_kernel<C, RED_THREADS><<<nblocks, RED_THREADS, 0, s>>>(
-                    blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, parts.as<pt>(), parts2.as<pt>());
-                msm_combine2_kernel<C, RED_THREADS><<<ncut, RED_THREADS, 0, s>>>(
-                    cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), parts2.as<pt>(), buckets.as<pt>());
-                G16_LAUNCHED(2);
-            }
-            G16_CUDA(cudaGetLastError());
+    // ---- accumulation + reductions, possibly on another stream
+    if (s_acc && s_acc != s) {
+        G16_CUDA(cudaStreamWaitEvent(s_acc, ev_t[2], 0));
+        s = s_acc;
+    }
+    G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
+    G16_CUDA(cudaEventRecord(ev_acc0, s));
+    const unsigned agrid = (nt_max + 127) / 128;
+    bool launched = false;
+    if constexpr (sizeof(pt) <= 128) {
+        if (acc_minb() == 4) {
+            msm_accumulate_kernel<C, 4><<<agrid, 128, 0, s>>>(bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(),
+                                                              t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
+            launched = true;
         }
     }
+    if (!launched)
+        msm_accumulate_kernel<C, 1><<<agrid, 128, 0, s>>>(bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(),
+                                                          t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
+    G16_CUDA(cudaEventRecord(ev_acc1, s));
+    const unsigned cgrid = (unsigned)std::min<size_t>((size_t(ncut_max) + 127) / 128, size_t(sms) * 4);
+    msm_combine_small_kernel<C><<<cgrid ? cgrid : 1, 128, 0, s>>>(cut_list.as<uint32_t>(), prm, part_base.as<uint32_t>(), parts.as<pt>(),
+                                                                  buckets.as<pt>());
+    msm_combine1_kernel<C, RED_THREADS><<<(unsigned)std::min<size_t>(nblk_max, size_t(sms) * 4), RED_THREADS, 0, s>>>(
+        blk_base.as<uint32_t>(), part_base.as<uint32_t>(), nb, prm, parts.as<pt>(), parts2.as<pt>());
+    msm_combine2_kernel<C, RED_THREADS><<<(unsigned)std::min<size_t>(ncut_max ? ncut_max : 1, size_t(sms) * 4), RED_THREADS, 0, s>>>(
+        cut_list.as<uint32_t>(), blk_base.as<uint32_t>(), prm, parts2.as<pt>(), buckets.as<pt>());
+    G16_CUDA(cudaGetLastError());
+    G16_LAUNCHED(4);
     uint32_t nchunks = uint32_t(W) * cpw, nchunks1 = uint32_t(W) * cpw1;
     msm_chunk_reduce_kernel<C, true, false><<<(nchunks + 63) / 64, 64, 0, s>>>(
         buckets.as<pt>(), bpw, L, cpw, nchunks, chunk_out.as<pt>(), chunk_sum.as<pt>());
@@ -1010,8 +894,9 @@ void Msm<C>::stage3(cudaStream_t s3) {
     G16_CUDA(cudaGetLastError());
     G16_LAUNCHED(3);
     G16_CUDA(cudaMemcpyAsync(h_windows, window_out.p, size_t(W) * sizeof(pt), cudaMemcpyDeviceToHost, s));
+    G16_CUDA(cudaMemcpyAsync(h_params, prm, sizeof(MsmParams), cudaMemcpyDeviceToHost, s));
     G16_CUDA(cudaEventRecord(ev_t[3], s));
-    stream = s;
+    enqueued = true;
 }
 #endif  // G16_MSM_INSTANTIATE
 

@@ -255,7 +255,7 @@ static void load_section(BaseSection<C>& sec, const Section& s, size_t rec, size
     if (table && sec.n) {
         // fixed-base window table (msm_window_table_kernel): on when asked for, or when it fits in a quarter of the
         // memory that is free right now
-        int c = msm_c ? (msm_c < 6 ? 6 : msm_c > 24 ? 24 : msm_c) : msm_pick_c_table(sec.n);
+        int c = msm_c ? (msm_c < 6 ? 6 : msm_c > 24 ? 24 : msm_c) : sparse ? msm_pick_c_table_sparse(sec.n) : msm_pick_c_table(sec.n);
         size_t need = Msm<C>::table_bytes(sec.n, c), free_b = 0, total_b = 0;
         G16_CUDA(cudaMemGetInfo(&free_b, &total_b));
         bool fits = size_t(msm_num_windows(c)) * sec.n <= size_t(MSM_INDEX_MASK);
@@ -328,11 +328,15 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
 
     // sections 5-9: base points (this shard's slice)
     size_t nv = zk->n_vars;
-    load_section<G1>(zk->A, need(secs, 5, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "5 (A)");
-    load_section<G1>(zk->B1, need(secs, 6, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "6 (B1)");
-    load_section<G2>(zk->B2, need(secs, 7, "zkey"), 128, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "7 (B2)");
+    // G16_W_TABLE=1: window tables for the witness-scalar sections too (one bucket set of wider windows: fewer digits per
+    // 64-bit and full-width wire); same memory rule as the H table
+    int w_table = 0;
+    if (const char* e = std::getenv("G16_W_TABLE")) w_table = std::atoi(e) > 0 ? 1 : 0;
+    load_section<G1>(zk->A, need(secs, 5, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "5 (A)", w_table);
+    load_section<G1>(zk->B1, need(secs, 6, "zkey"), 64, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "6 (B1)", w_table);
+    load_section<G2>(zk->B2, need(secs, 7, "zkey"), 128, nv, zk->shard_rank, zk->shard_count, o.msm_c, true, st, "7 (B2)", w_table);
     load_section<G1>(zk->C, need(secs, 8, "zkey"), 64, nv - zk->n_public - 1, zk->shard_rank, zk->shard_count, o.msm_c,
-                     true, st, "8 (C)");
+                     true, st, "8 (C)", w_table);
     // H scalars are dense (every window of every scalar is live): the one section where a window table pays.
     // opts.h_table / G16_H_TABLE: 1 = always, -1 = never, 0 = when it fits (see load_section)
     int h_table = o.h_table;
@@ -542,78 +546,68 @@ struct JoinedSlices {
     const fe_t *a, *b, *c;
 };
 
-// the device part of a proof: five partial MSM sums of this shard, left in the Msm objects' host buffers
+// the device part of a proof: five partial MSM sums of this shard, left in the Msm objects' host buffers.
+// The whole proof is ONE enqueue: no host thread and no read-back of a counter sits between the kernels (the MSMs size
+// their launches from device memory, msm.cuh); the host only waits for the five results at the end, in the order they
+// finish, and runs each finished MSM's window Horner chain while the others still compute.
 static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
     if (!zk->witness_loaded) throw std::runtime_error("no witness loaded");
     G16_CUDA(cudaSetDevice(zk->device));
     auto t0 = std::chrono::steady_clock::now();
     const uint32_t* w = zk->w.as<uint32_t>();
-    G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
-    // witness-scalar MSMs start at once; the H MSM waits for the NTT pipeline
-    for (int i = 0; i < 4; i++) {
-        G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], zk->ev[0], 0));
-        G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_pre[i]));
-    }
-    zk->A.msm.stage1(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_pre[0]);
-    zk->B1.msm.stage1(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_pre[1]);
-    zk->B2.msm.stage1(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2]);
-    zk->C.msm.stage1(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8,
-                     zk->C.mask.as<uint32_t>(), zk->C.n, zk->s_pre[3]);
-    if (js) {
-        G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
-        if (zk->H.n) {
-            ntt_join_kernel<<<(unsigned)((zk->H.n + 255) / 256), 256, 0, zk->s_main>>>(
-                js->a, js->b, js->c, zk->pa.as<fe_t>() + zk->H.lo, (uint32_t)zk->H.n);
-            G16_CUDA(cudaGetLastError());
-            G16_LAUNCHED(1);
-        }
-        G16_CUDA(cudaEventRecord(zk->ev[2], zk->s_main));
-    } else {
-        enqueue_h_pipeline(zk);
-    }
-    // H digits + sort stay on the transform stream (highest priority, already ordered after the join); only the
-    // accumulation and reductions move to the lowest-priority stream (Msm::stage3)
-    G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
-    zk->H.msm.stage1(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
-                     zk->s_main);
-    // Each MSM has two points where the host must read a counter back (entry count, task count).  One host thread
-    // per MSM drives those, so a wait on one stream never delays the launches of another (the H chain in particular
-    // must be enqueued the moment the transforms finish).
-    int dev = zk->device;
-    // G16_ACC_AFTER_NTT=1 (experiment): the witness accumulations wait for the transforms, so that the transforms run
-    // with only HBM-bound sorts beside them and the accumulations fill the integer pipe while the H entries are sorted
-    static const bool acc_after_ntt = [] { const char* e = std::getenv("G16_ACC_AFTER_NTT"); return e && std::atoi(e) != 0; }();
-    cudaEvent_t ntt_done = zk->ev[2];
-    auto drive = [dev, ntt_done](auto* msm, cudaStream_t st, cudaEvent_t done, bool gate) {
-        G16_CUDA(cudaSetDevice(dev));
-        msm->stage2();
-        if (gate) G16_CUDA(cudaStreamWaitEvent(st, ntt_done, 0));
-        msm->stage3(st);
-        G16_CUDA(cudaEventRecord(done, st));
-        G16_CUDA(cudaStreamSynchronize(st));
-    };
-    // the witness MSMs finish while the H accumulation still runs: their window Horner chains (255 doublings each, on
-    // the host) are done right here, off the critical path; only the H chain is left for export_partial
-    auto f0 = std::async(std::launch::async, [&] { drive(&zk->A.msm, zk->s_msm[0], zk->ev[4], acc_after_ntt); zk->fin_a = zk->A.msm.finish<HG1>(); });
-    auto f1 = std::async(std::launch::async, [&] { drive(&zk->B1.msm, zk->s_msm[1], zk->ev[6], acc_after_ntt); zk->fin_b1 = zk->B1.msm.finish<HG1>(); });
-    auto f2 = std::async(std::launch::async, [&] { drive(&zk->B2.msm, zk->s_msm[2], zk->ev[8], acc_after_ntt); zk->fin_b2 = zk->B2.msm.finish<HG2>(); });
-    auto f3 = std::async(std::launch::async, [&] { drive(&zk->C.msm, zk->s_msm[3], zk->ev[10], acc_after_ntt); zk->fin_c = zk->C.msm.finish<HG1>(); });
-    std::exception_ptr err;
     try {
-        drive(&zk->H.msm, zk->s_msm[4], zk->ev[12], false);
-    } catch (...) {
-        err = std::current_exception();
-    }
-    for (auto* f : {&f0, &f1, &f2, &f3}) {
-        try {
-            f->get();
-        } catch (...) {
-            if (!err) err = std::current_exception();
+        G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
+        // witness-scalar MSMs start at once; the H MSM waits for the NTT pipeline.  Preparation (counting sort of the
+        // digits, HBM-bound and short) on streams of the transforms' priority so that it interleaves with the
+        // integer-bound transforms; accumulations + reductions at middle priority.  B2 first: its G2 reductions are the
+        // longest latency-bound tail.
+        for (int i = 0; i < 4; i++) {
+            G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], zk->ev[0], 0));
+            G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_pre[i]));
         }
+        zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2], zk->s_msm[2]);
+        G16_CUDA(cudaEventRecord(zk->ev[8], zk->s_msm[2]));
+        zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_pre[0], zk->s_msm[0]);
+        G16_CUDA(cudaEventRecord(zk->ev[4], zk->s_msm[0]));
+        zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_pre[1], zk->s_msm[1]);
+        G16_CUDA(cudaEventRecord(zk->ev[6], zk->s_msm[1]));
+        zk->C.msm.enqueue(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8, zk->C.mask.as<uint32_t>(), zk->C.n,
+                          zk->s_pre[3], zk->s_msm[3]);
+        G16_CUDA(cudaEventRecord(zk->ev[10], zk->s_msm[3]));
+        if (js) {
+            G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
+            if (zk->H.n) {
+                ntt_join_kernel<<<(unsigned)((zk->H.n + 255) / 256), 256, 0, zk->s_main>>>(
+                    js->a, js->b, js->c, zk->pa.as<fe_t>() + zk->H.lo, (uint32_t)zk->H.n);
+                G16_CUDA(cudaGetLastError());
+                G16_LAUNCHED(1);
+            }
+            G16_CUDA(cudaEventRecord(zk->ev[2], zk->s_main));
+        } else {
+            enqueue_h_pipeline(zk);
+        }
+        // H: preparation stays on the transform stream (highest priority, already ordered after the join); only the
+        // accumulation and reductions move to the lowest-priority stream, filling the machine under everything else
+        G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
+        zk->H.msm.enqueue(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
+                          zk->s_main, zk->s_msm[4]);
+        G16_CUDA(cudaEventRecord(zk->ev[12], zk->s_msm[4]));
+        // results, in the order they are expected to finish; each finished MSM's Horner chain (255 doublings on the
+        // host) overlaps the MSMs still running
+        zk->A.msm.wait();  zk->fin_a = zk->A.msm.finish<HG1>();
+        zk->B1.msm.wait(); zk->fin_b1 = zk->B1.msm.finish<HG1>();
+        zk->C.msm.wait();  zk->fin_c = zk->C.msm.finish<HG1>();
+        zk->B2.msm.wait(); zk->fin_b2 = zk->B2.msm.finish<HG2>();
+        zk->H.msm.wait();
+        for (int i = 0; i < 5; i++) G16_CUDA(cudaStreamSynchronize(zk->s_msm[i]));
+        G16_CUDA(cudaStreamSynchronize(zk->s_main));
+    } catch (...) {
+        // a failed enqueue leaves kernels of this proof in flight on other streams: drain them before the handle is
+        // reused (the service keeps a key resident after a failed proof), and forget the half-made results
+        cudaDeviceSynchronize();
+        zk->partial_done = false;
+        throw;
     }
-    if (err) std::rethrow_exception(err);
-    for (int i = 0; i < 5; i++) G16_CUDA(cudaStreamSynchronize(zk->s_msm[i]));
-    G16_CUDA(cudaStreamSynchronize(zk->s_main));
     float ms = 0;
     cudaEventElapsedTime(&ms, zk->ev[0], zk->ev[1]); zk->t_ms[1] = ms;
     cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_ms[2] = ms;
