@@ -4,7 +4,7 @@ CSRC     := $(PKG)/csrc
 NVCC     ?= nvcc
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
-OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o $(CSRC)/verify.o
+OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o $(CSRC)/poseidon.o $(CSRC)/verify.o $(CSRC)/merkle.o
 HDRS     := $(wildcard $(CSRC)/*.cuh) $(filter-out $(CSRC)/service% $(CSRC)/verify%,$(wildcard $(CSRC)/*.hpp)) include/g16_b200.h
 
 all: $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover
@@ -13,6 +13,9 @@ $(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 
 $(CSRC)/verify.o: $(CSRC)/verify.cpp $(wildcard $(CSRC)/verify*.hpp) $(CSRC)/hostfield.hpp include/g16_b200.h
+	g++ -O2 -std=c++17 -fPIC -Wall -Iinclude -c $< -o $@
+
+$(CSRC)/merkle.o: $(CSRC)/merkle.cpp $(wildcard $(CSRC)/verify*.hpp) $(CSRC)/hostfield.hpp include/g16_b200.h
 	g++ -O2 -std=c++17 -fPIC -Wall -Iinclude -c $< -o $@
 
 $(PKG)/libg16b200.so: $(OBJS)

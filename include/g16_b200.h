@@ -179,6 +179,32 @@ unsigned long long g16_launch_count(void);
  * Returns achieved ops per second over the whole device (op 2: field products per second). */
 int g16_bench_int_pipe(int op, double* ops_per_s);
 
+
+/* ---- Poseidon Merkle tree of the anonymity set ------------------------------------------
+ * Replaces the reference's scripts/merkle_tree.rs (`merkle-tree` binary run by scripts/full_workflow.sh:371-381):
+ * hasher = light_poseidon Poseidon::<Fr>::new_circom(2) (merkle_tree.rs:150-181, the circomlib Poseidon(2) of
+ * circuits/merkle.circom:39), leaf = hash(address, balance) + zero leaves up to a power of two (:206-269), proofs =
+ * siblings bottom-up with the index bits (:290-396).  Field elements are 32-byte little-endian STANDARD form and must
+ * be below r.  All hashing runs on the GPU; there is no CPU fallback. */
+typedef struct g16_merkle g16_merkle;
+/* out[i] = Poseidon(pairs[2i], pairs[2i+1]) for n pairs of host memory */
+int g16_poseidon_hash2(const uint8_t* pairs, size_t n, uint8_t* out, const g16_opts* opts);
+/* rows: n_rows x (address[32] | balance[32]); builds the whole tree and keeps it on the device */
+int g16_merkle_build(const uint8_t* rows, size_t n_rows, const g16_opts* opts, g16_merkle** out);
+void g16_merkle_close(g16_merkle* t);
+/* levels = node levels including leaves and root (the number merkle_tree.rs prints as "height") */
+int g16_merkle_info(const g16_merkle* t, uint64_t* n_rows, uint64_t* n_leaves, uint32_t* levels, double* build_ms);
+int g16_merkle_root(const g16_merkle* t, uint8_t out[32]);
+int g16_merkle_node(const g16_merkle* t, uint32_t level, uint64_t index, uint8_t out[32]);
+/* path_elements: (levels-1) x 32 bytes, path_indices: levels-1 bytes (0 = the node is a left child) */
+int g16_merkle_proof(const g16_merkle* t, uint64_t index, uint8_t* path_elements, uint8_t* path_indices);
+/* first leaf index >= from whose hash equals `hash`, UINT64_MAX if none (the reference's forward scan, :315-335) */
+int g16_merkle_find(const g16_merkle* t, const uint8_t hash[32], uint64_t from, uint64_t* index);
+/* the whole `merkle-tree --anon-set <csv> --poa-input-data <json> --output-dir <dir>` command: writes
+ * <dir>/merkle_root.json and <dir>/merkle_proofs.json in the reference's byte layout (scripts/README.md:633-673).
+ * poa_input_json may be NULL (root only, empty proofs file). */
+int g16_merkle_files(const char* anon_set_csv, const char* poa_input_json, const char* output_dir, const g16_opts* opts);
+
 #ifdef __cplusplus
 }
 #endif

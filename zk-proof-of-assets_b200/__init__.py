@@ -38,6 +38,8 @@ ABI_SYMBOLS = [
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
     "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace", "g16_h_transform", "g16_h_buffer",
     "g16_prove_partial_joined", "g16_verify", "g16_sanitize",
+    "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
+    "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -119,6 +121,16 @@ def lib():
                                    ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_verify.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
                                  ctypes.c_size_t, ctypes.c_void_p]
+        L.g16_poseidon_hash2.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_merkle_build.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_merkle_close.argtypes = [ctypes.c_void_p]
+        L.g16_merkle_close.restype = None
+        L.g16_merkle_info.argtypes = [ctypes.c_void_p] * 5
+        L.g16_merkle_root.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_merkle_node.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint64, ctypes.c_void_p]
+        L.g16_merkle_proof.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_merkle_find.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p]
+        L.g16_merkle_files.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -464,6 +476,80 @@ def bench_int_pipe(op):
     v = ctypes.c_double()
     _check(lib().g16_bench_int_pipe(op, ctypes.byref(v)))
     return v.value
+
+
+# ---- Poseidon Merkle tree of the anonymity set (scripts/merkle_tree.rs) -----------------------------------------
+def poseidon_hash2(pairs, device=-1):
+    """pairs = [(a, b)] ints below r -> [Poseidon(a, b)] (circomlib Poseidon(2)), hashed on the GPU"""
+    n = len(pairs)
+    buf = b"".join(int(a).to_bytes(32, "little") + int(b).to_bytes(32, "little") for a, b in pairs)
+    out = ctypes.create_string_buffer(32 * max(n, 1))
+    o = make_opts(device=device)
+    _check(lib().g16_poseidon_hash2(_addr(buf) if n else None, n, out, ctypes.byref(o)))
+    return [int.from_bytes(out.raw[32 * i:32 * i + 32], "little") for i in range(n)]
+
+
+class MerkleTree:
+    """The anonymity-set tree, built and kept on one GPU.  rows = [(address, balance)] ints, or the packed bytes
+    (n x (address[32] | balance[32]), little-endian)."""
+
+    def __init__(self, rows, device=-1):
+        self._h = ctypes.c_void_p()
+        if not isinstance(rows, (bytes, bytearray, memoryview)) and not hasattr(rows, "ctypes"):
+            rows = b"".join(int(a).to_bytes(32, "little") + int(b).to_bytes(32, "little") for a, b in rows)
+        n = (rows.nbytes if hasattr(rows, "nbytes") else len(rows)) // 64
+        o = make_opts(device=device)
+        _check(lib().g16_merkle_build(_addr(rows) if n else None, n, ctypes.byref(o), ctypes.byref(self._h)))
+        nr, nl, lv, ms = ctypes.c_uint64(), ctypes.c_uint64(), ctypes.c_uint32(), ctypes.c_double()
+        _check(lib().g16_merkle_info(self._h, ctypes.byref(nr), ctypes.byref(nl), ctypes.byref(lv), ctypes.byref(ms)))
+        self.n_rows, self.n_leaves, self.levels, self.build_ms = nr.value, nl.value, lv.value, ms.value
+
+    def root(self):
+        out = ctypes.create_string_buffer(32)
+        _check(lib().g16_merkle_root(self._h, out))
+        return int.from_bytes(out.raw, "little")
+
+    def node(self, level, index):
+        out = ctypes.create_string_buffer(32)
+        _check(lib().g16_merkle_node(self._h, level, index, out))
+        return int.from_bytes(out.raw, "little")
+
+    def proof(self, index):
+        """-> (path_elements bottom-up, path_indices)"""
+        k = self.levels - 1
+        el, ix = ctypes.create_string_buffer(32 * max(k, 1)), ctypes.create_string_buffer(max(k, 1))
+        _check(lib().g16_merkle_proof(self._h, index, el, ix))
+        return [int.from_bytes(el.raw[32 * i:32 * i + 32], "little") for i in range(k)], list(ix.raw[:k])
+
+    def find(self, leaf_hash, start=0):
+        """first leaf index >= start holding leaf_hash, or None"""
+        idx = ctypes.c_uint64()
+        _check(lib().g16_merkle_find(self._h, int(leaf_hash).to_bytes(32, "little"), start, ctypes.byref(idx)))
+        return None if idx.value == (1 << 64) - 1 else idx.value
+
+    def close(self):
+        if self._h:
+            lib().g16_merkle_close(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def merkle_files(anon_set_csv, poa_input_json, output_dir, device=-1):
+    """`merkle-tree --anon-set .. --poa-input-data .. --output-dir ..` (scripts/full_workflow.sh:371-381) as one call"""
+    o = make_opts(device=device)
+    _check(lib().g16_merkle_files(os.fsencode(anon_set_csv), os.fsencode(poa_input_json) if poa_input_json else None,
+                                  os.fsencode(output_dir), ctypes.byref(o)))
 
 
 # ---- SYNTH-1 fixtures (bench/test support) ------------------------------------------------------------------

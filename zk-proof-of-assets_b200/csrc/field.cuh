@@ -351,6 +351,64 @@ struct Fq2 {
     }
 };
 
+// ---- Fq2 split over a pair of lanes ---------------------------------------------------------------------------
+// Lanes (2k, 2k+1) of a warp hold ONE Fq2 element: the even lane its c0, the odd lane its c1.  Every operation is
+// called by both lanes of the pair together (control flow must be uniform within a pair); halves are exchanged with
+// shuffles under the pair's own two-lane mask, so different pairs of a warp may sit in different branches.
+// Why: a G2 XYZZ accumulator is 64 registers per thread in the one-thread form (255 registers + stack, 2 CTAs per SM,
+// 58 % pipe utilisation); split, a thread holds 32 and the kernel fits the G1 budget (128 registers, 4 CTAs per SM).
+// Cost: the product is the 4-multiplication schoolbook form, two per lane (Karatsuba's three do not split evenly),
+// the squaring stays one per lane.
+struct Fq2Half {
+    typedef fe_t el;
+    static __device__ __forceinline__ uint32_t half() { return threadIdx.x & 1u; }
+    static __device__ __forceinline__ uint32_t pair_mask() { return 3u << (threadIdx.x & 30u); }
+    static __device__ __forceinline__ el other(const el& a) {
+        el o;
+        const uint32_t m = pair_mask();
+#pragma unroll
+        for (int i = 0; i < 8; i++) o.v[i] = __shfl_xor_sync(m, a.v[i], 1);
+        return o;
+    }
+    static __device__ __forceinline__ el zero() { return Fq::zero(); }
+    static __device__ __forceinline__ el one() { return half() ? Fq::zero() : Fq::one(); }
+    static __device__ __forceinline__ bool is_zero(const el& a) {
+        bool z = Fq::is_zero(a);
+        bool oz = __shfl_xor_sync(pair_mask(), (int)z, 1) != 0;
+        return z && oz;
+    }
+    static __device__ __forceinline__ bool eq(const el& a, const el& b) {
+        bool z = Fq::eq(a, b);
+        bool oz = __shfl_xor_sync(pair_mask(), (int)z, 1) != 0;
+        return z && oz;
+    }
+    static __device__ __forceinline__ el add(const el& a, const el& b) { return Fq::add(a, b); }
+    static __device__ __forceinline__ el sub(const el& a, const el& b) { return Fq::sub(a, b); }
+    static __device__ __forceinline__ el dbl(const el& a) { return Fq::dbl(a); }
+    static __device__ __forceinline__ el neg(const el& a) { return Fq::neg(a); }
+    // (a0 + a1 u)(b0 + b1 u) = (a0 b0 - a1 b1) + (a0 b1 + a1 b0) u
+    static __device__ __forceinline__ el mul(const el& a, const el& b) {
+        const uint32_t h = half();
+        el ob = other(b);
+        el same = Fq::mul(a, b);      // lane 0: a0 b0, lane 1: a1 b1
+        el cross = Fq::mul(a, ob);    // lane 0: a0 b1, lane 1: a1 b0
+        el send;
+#pragma unroll
+        for (int i = 0; i < 8; i++) send.v[i] = h ? same.v[i] : cross.v[i];
+        el recv = other(send);        // lane 0 gets a1 b1, lane 1 gets a0 b1
+        return h ? Fq::add(cross, recv) : Fq::sub(same, recv);
+    }
+    // c0 = (a0 + a1)(a0 - a1), c1 = 2 a0 a1: one product per lane
+    static __device__ __forceinline__ el sqr(const el& a) {
+        const uint32_t h = half();
+        el oa = other(a);
+        el u = h ? a : Fq::add(a, oa);
+        el v = h ? oa : Fq::sub(a, oa);
+        el r = Fq::mul(u, v);
+        return h ? Fq::dbl(r) : r;
+    }
+};
+
 // 32-byte element load/store as two 16-byte vector accesses
 __device__ __forceinline__ fe_t ld_fe(const fe_t* p) {
     const uint4* q = reinterpret_cast<const uint4*>(p);

@@ -357,6 +357,50 @@ msm_accumulate_kernel(const typename C::aff* __restrict__ bases, const uint32_t*
     else buckets[out] = acc;
 }
 
+// The G2 accumulation over lane pairs (Fq2Half, field.cuh): lanes (2k, 2k+1) run ONE task, the even lane on the c0
+// halves of every coordinate, the odd lane on the c1 halves.  Same registers per thread as the G1 kernel (32 for the
+// accumulator, 16 + 16 for the point and the prefetched one), so 4 CTAs per SM instead of 2 and no stack.
+__global__ void __launch_bounds__(128, 4)
+msm_accumulate_g2_pair_kernel(const g2_aff* __restrict__ bases, const uint32_t* __restrict__ vals,
+                              const uint32_t* __restrict__ order, const uint32_t* __restrict__ t_begin,
+                              const uint32_t* __restrict__ t_len, const uint32_t* __restrict__ t_out,
+                              const MsmParams* __restrict__ prm, g2_pt* __restrict__ buckets, g2_pt* __restrict__ parts) {
+    typedef Curve<Fq2Half> CH;
+    uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t task = tid >> 1;
+    const uint32_t h = tid & 1u;
+    if (task >= prm->nt) return;   // uniform within a pair
+    uint32_t j = order[task];
+    uint32_t e = t_begin[j], len = t_len[j], out = t_out[j];
+    auto fetch = [&](uint32_t v) {   // record = x.c0 x.c1 y.c0 y.c1
+        const fe_t* rec = reinterpret_cast<const fe_t*>(bases + (v & MSM_INDEX_MASK));
+        CH::aff a;
+        a.x = ldg_fe(rec + h);
+        a.y = ldg_fe(rec + 2 + h);
+        return a;
+    };
+    CH::pt acc = CH::identity();
+    uint32_t v = vals[e];
+    CH::aff q = fetch(v);
+    for (uint32_t k = 0; k < len; k++) {
+        uint32_t vn = 0;
+        CH::aff qn = q;
+        if (k + 1 < len) {
+            vn = vals[e + k + 1];
+            qn = fetch(vn);
+        }
+        if (v >> 31) q.y = Fq::neg(q.y);
+        CH::madd(acc, q);
+        v = vn;
+        q = qn;
+    }
+    fe_t* o = reinterpret_cast<fe_t*>((out >> 31) ? parts + (out & 0x7fffffffu) : buckets + out);
+    st_fe(o + h, acc.x);
+    st_fe(o + 2 + h, acc.y);
+    st_fe(o + 4 + h, acc.zz);
+    st_fe(o + 6 + h, acc.zzz);
+}
+
 // Most cut buckets hold a handful of partial sums (a bucket a few times over the task size): one thread each.
 template <class C>
 __global__ void __launch_bounds__(128)
@@ -627,8 +671,9 @@ public:
     // `s`; the accumulation and the reductions on `s_acc` (nullptr = the same stream): the prover keeps the H MSM's
     // preparation on the high-priority transform stream and its accumulation on the lowest-priority one, so that it
     // fills the machine under everything else.  scalars/bases/mask are device pointers; n <= reserved capacity.
+    // `gate` (optional): an event the accumulation waits for (scheduling: see prove_device).
     void enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s,
-                 cudaStream_t s_acc = nullptr);
+                 cudaStream_t s_acc = nullptr, cudaEvent_t gate = nullptr);
 
     // block until the window sums and counters of the last enqueue() are in host memory
     void wait() {
@@ -786,7 +831,7 @@ size_t Msm<C>::build_table(const aff* bases_, size_t n_, cudaStream_t s) {
 
 template <class C>
 void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s,
-                     cudaStream_t s_acc) {
+                     cudaStream_t s_acc, cudaEvent_t gate) {
     if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
     if (cfg.table && n_ != table_n) throw std::runtime_error("MSM: window table was built for a different base count");
     bases = cfg.table && n_ ? table.template as<aff>() : bases_;
@@ -842,10 +887,21 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
         G16_CUDA(cudaStreamWaitEvent(s_acc, ev_t[2], 0));
         s = s_acc;
     }
+    if (gate) G16_CUDA(cudaStreamWaitEvent(s, gate, 0));
     G16_CUDA(cudaMemsetAsync(buckets.p, 0, size_t(nb) * sizeof(pt), s));
     G16_CUDA(cudaEventRecord(ev_acc0, s));
     const unsigned agrid = (nt_max + 127) / 128;
     bool launched = false;
+    if constexpr (sizeof(pt) > 128) {
+        // G2: one task per lane pair (G16_G2_PAIR=0 selects the one-thread kernel for comparison)
+        static const bool pair = [] { const char* e = std::getenv("G16_G2_PAIR"); return !e || std::atoi(e) != 0; }();
+        if (pair) {
+            msm_accumulate_g2_pair_kernel<<<(2 * nt_max + 127) / 128, 128, 0, s>>>(
+                bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm,
+                buckets.as<pt>(), parts.as<pt>());
+            launched = true;
+        }
+    }
     if constexpr (sizeof(pt) <= 128) {
         if (acc_minb() == 4) {
             msm_accumulate_kernel<C, 4><<<agrid, 128, 0, s>>>(bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(),

@@ -315,8 +315,13 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     int prio_mid = prio_hi < prio_lo - 1 ? prio_hi + 1 : prio_hi;
     G16_CUDA(cudaStreamCreateWithPriority(&zk->s_main, cudaStreamNonBlocking, prio_hi));
+    // G16_HPRIO (scheduling experiment): priority of the H accumulation stream, 0 = lowest (default), 1 = middle, 2 = highest
+    static const int hprio = [] { const char* e = std::getenv("G16_HPRIO"); return e ? std::atoi(e) : 0; }();
+    int prio_h = hprio == 2 ? prio_hi : hprio == 1 ? prio_mid : prio_lo;
+    // with the H accumulation above them, the witness accumulations drop to the lowest priority (they become the filler)
+    int prio_w = hprio == 2 ? prio_lo : prio_mid;
     for (int i = 0; i < 5; i++)
-        G16_CUDA(cudaStreamCreateWithPriority(&zk->s_msm[i], cudaStreamNonBlocking, i == 4 ? prio_lo : prio_mid));
+        G16_CUDA(cudaStreamCreateWithPriority(&zk->s_msm[i], cudaStreamNonBlocking, i == 4 ? prio_h : prio_w));
     // digits + sort of the witness MSMs are HBM-bound and short; at the transforms' priority they interleave with the
     // (integer-bound) transforms instead of being starved by them, so the accumulations are ready when the transforms end
     for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamCreateWithPriority(&zk->s_pre[i], cudaStreamNonBlocking, prio_hi));
@@ -565,15 +570,27 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
             G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], zk->ev[0], 0));
             G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_pre[i]));
         }
-        zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2], zk->s_msm[2]);
+        // G16_GATE (scheduling experiment): bit 0 = the G1 witness accumulations wait for the transforms, bit 1 = B2 too.
+        // The transforms then run without long-lived accumulation CTAs in their way, at the price of idle pipe slots.
+        static const int gate_mask = [] { const char* e = std::getenv("G16_GATE"); return e ? std::atoi(e) : 0; }();
+        const bool deferred = (gate_mask & 4) != 0;   // bit 2: enqueue the witness MSMs after the H chain
+        cudaEvent_t ntt_done = zk->ev[2];
+        auto witness_msms = [&]() {
+        if ((gate_mask & 8) && !deferred)   // bit 3: the witness MSMs' preparation waits for the transforms as well
+            for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], ntt_done, 0));
+        zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2], zk->s_msm[2],
+                           (gate_mask & 2) && !deferred ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[8], zk->s_msm[2]));
-        zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_pre[0], zk->s_msm[0]);
+        zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_pre[0], zk->s_msm[0],
+                          (gate_mask & 1) && !deferred ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[4], zk->s_msm[0]));
-        zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_pre[1], zk->s_msm[1]);
+        zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_pre[1], zk->s_msm[1],
+                           (gate_mask & 1) && !deferred ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[6], zk->s_msm[1]));
         zk->C.msm.enqueue(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8, zk->C.mask.as<uint32_t>(), zk->C.n,
-                          zk->s_pre[3], zk->s_msm[3]);
+                          zk->s_pre[3], zk->s_msm[3], (gate_mask & 1) && !deferred ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[10], zk->s_msm[3]));
+        };
         if (js) {
             G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
             if (zk->H.n) {
@@ -586,12 +603,14 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         } else {
             enqueue_h_pipeline(zk);
         }
+        if (!deferred) witness_msms();   // after the transforms are enqueued: ev[2] is this proof's record
         // H: preparation stays on the transform stream (highest priority, already ordered after the join); only the
         // accumulation and reductions move to the lowest-priority stream, filling the machine under everything else
         G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
         zk->H.msm.enqueue(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
                           zk->s_main, zk->s_msm[4]);
         G16_CUDA(cudaEventRecord(zk->ev[12], zk->s_msm[4]));
+        if (deferred) witness_msms();
         // results, in the order they are expected to finish; each finished MSM's Horner chain (255 doublings on the
         // host) overlaps the MSMs still running
         zk->A.msm.wait();  zk->fin_a = zk->A.msm.finish<HG1>();

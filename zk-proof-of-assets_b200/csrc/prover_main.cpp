@@ -13,6 +13,8 @@
 //     prover --verify <verification_key.json> <public.json> <proof.json>     exit 0 + "OK!" | exit 1 + "Invalid proof"
 //     prover --sanitize <verification_key.json> <public.json> <proof.json> <sanitized_proof.json>
 //                                   the limb file scripts/sanitize_groth16_proof.py:112-123 writes, byte for byte
+// Anonymity-set Merkle tree (the argv of the reference's `merkle-tree`, scripts/merkle_tree.rs:29-44):
+//     prover --merkle-tree --anon-set <csv> --poa-input-data <json> --output-dir <dir>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
@@ -110,7 +112,33 @@ static int verify_cli(int argc, char** argv) {
     return ok ? 0 : 1;
 }
 
+// `merkle-tree` of the reference (scripts/merkle_tree.rs:29-44): -a/--anon-set, -p/--poa-input-data, -o/--output-dir
+static int merkle_cli(int argc, char** argv) {
+    const char *anon = nullptr, *poa = nullptr, *out = nullptr;
+    for (int i = 2; i < argc; i++) {
+        std::string a = argv[i];
+        if ((a == "-a" || a == "--anon-set") && i + 1 < argc) anon = argv[++i];
+        else if ((a == "-p" || a == "--poa-input-data") && i + 1 < argc) poa = argv[++i];
+        else if ((a == "-o" || a == "--output-dir") && i + 1 < argc) out = argv[++i];
+        else {
+            std::fprintf(stderr, "Usage: prover --merkle-tree --anon-set <FILE_PATH> --poa-input-data <FILE_PATH> --output-dir <DIR_PATH>\n");
+            return 2;
+        }
+    }
+    if (!anon || !out) {
+        std::fprintf(stderr, "Usage: prover --merkle-tree --anon-set <FILE_PATH> --poa-input-data <FILE_PATH> --output-dir <DIR_PATH>\n");
+        return 2;
+    }
+    int rc = g16_merkle_files(anon, poa, out, nullptr);
+    if (rc != G16_OK) {
+        std::fprintf(stderr, "%s\n", g16_last_error());
+        return 1;
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc >= 2 && !std::strcmp(argv[1], "--merkle-tree")) return merkle_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--verify") || !std::strcmp(argv[1], "--sanitize"))) return verify_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--serve") || !std::strcmp(argv[1], "--ping") ||
                       !std::strcmp(argv[1], "--stats") || !std::strcmp(argv[1], "--shutdown")))
