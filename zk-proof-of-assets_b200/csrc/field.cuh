@@ -9,7 +9,7 @@
 // 32x32->64 product lands on an aligned register pair and a row is four carry chains of
 // mad.lo.cc/madc.hi.cc (ptxas pairs them into IMAD.WIDE.U32 + carry).  128 wide MADs + 8 single
 // MULs per product = the 136-op work model of SURVEY.md section 8(d).  The design was checked limb for
-// limb by scratch/montsim.py before it was written here.
+// limb by tools/montsim.py before it was written here.
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>

@@ -23,6 +23,7 @@
 #pragma once
 #include <cub/cub.cuh>
 #include <algorithm>
+#include <climits>
 #include <cstdlib>
 #include <cstring>
 #include <stdexcept>
@@ -193,6 +194,55 @@ msm_window_table_kernel(const typename C::aff* __restrict__ bases, uint32_t n, i
         t.y = F::mul(t.y, u);
         table[size_t(w) * n + i] = t;
     }
+}
+
+// Dense uniform scalars over a window table (the H MSM): nearly every window of every scalar is a live digit, so the
+// entry count is known up front to within 2^-c: digit w of scalar i goes to the FIXED slot w * n + i (coalesced stores,
+// no atomics), dead digits carry the sentinel key nb, and a radix sort of all n * W slots (a count the host knows, so
+// still no read-back) brings the buckets together with the sentinels at the end.  The counting sort above needs one
+// returning atomic and one scattered 4-byte store per entry, which at 2^24 scalars (2 x 10^8 entries) is 3 x slower
+// than the radix sort's streaming passes.
+static __global__ void __launch_bounds__(256)
+msm_digits_dense_kernel(const uint32_t* __restrict__ scalars, uint32_t n, const uint32_t* __restrict__ inf_mask, int c, int W,
+                        uint32_t nb, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t half = 1u << (c - 1);
+    const uint32_t mask = (1u << c) - 1;
+    uint32_t s[8];
+    bool live = !(inf_mask && ((inf_mask[i >> 5] >> (i & 31)) & 1));
+    {
+        const uint4* p = reinterpret_cast<const uint4*>(scalars + size_t(i) * 8);
+        uint4 a = p[0], b = p[1];
+        s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+    }
+    uint32_t carry = 0;
+    for (int w = 0; w < W; w++) {
+        int bit = w * c, limb = bit >> 5, sh = bit & 31;
+        unsigned long long v = limb < 8 ? s[limb] : 0;
+        if (limb + 1 < 8) v |= (unsigned long long)s[limb + 1] << 32;
+        uint32_t d = (uint32_t)((v >> sh) & mask) + carry;
+        carry = d > half;
+        bool nz = live && d != 0 && d != (1u << c);
+        uint32_t neg = carry;
+        uint32_t mag = neg ? (1u << c) - d : d;
+        size_t slot = size_t(w) * n + i;
+        keys[slot] = nz ? mag - 1 : nb;
+        vals[slot] = ((uint32_t)w * n + i) | (neg << 31);
+    }
+}
+
+// start[k] = first position of key k in the sorted keys (lower bound), k = 0 .. nb; start[nb] = live entries
+static __global__ void msm_lower_bound_kernel(const uint32_t* __restrict__ keys, uint32_t m, uint32_t nb, uint32_t* __restrict__ start) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > nb) return;
+    uint32_t lo = 0, hi = m;
+    while (lo < hi) {
+        uint32_t mid = lo + ((hi - lo) >> 1);
+        if (keys[mid] < k) lo = mid + 1;
+        else hi = mid;
+    }
+    start[k] = lo;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -672,8 +722,11 @@ public:
     // preparation on the high-priority transform stream and its accumulation on the lowest-priority one, so that it
     // fills the machine under everything else.  scalars/bases/mask are device pointers; n <= reserved capacity.
     // `gate` (optional): an event the accumulation waits for (scheduling: see prove_device).
+    // `s_red` (optional): a third stream for what follows the accumulation kernel (combine, bucket reduction, copies to
+    // the host): latency-bound work on few threads, which the prover puts on high-priority side streams while the
+    // accumulation kernels of all five MSMs run back to back on one stream.
     void enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s,
-                 cudaStream_t s_acc = nullptr, cudaEvent_t gate = nullptr);
+                 cudaStream_t s_acc = nullptr, cudaEvent_t gate = nullptr, cudaStream_t s_red = nullptr);
 
     // block until the window sums and counters of the last enqueue() are in host memory
     void wait() {
@@ -732,7 +785,7 @@ private:
     uint32_t bpw = 0, nb = 0, cpw = 0, cpw1 = 0, ns0 = 0, ns1 = 0;
     uint32_t nt_max = 0, np_max = 0, nblk_max = 0, ncut_max = 0;
     const aff* bases = nullptr;
-    DevBuf vals, count, start, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
+    DevBuf vals, keys_a, keys_b, vals_b, count, start, ntasks, nparts, nblk, task_base, part_base, blk_base, cut_list,
         t_begin, t_len, t_out, order, hist, buckets, parts, parts2, chunk_out, chunk_sum, chunk2_out, slice_out,
         slice1_out, window_out, params, cub_tmp, table;
     size_t table_n = 0;
@@ -740,6 +793,14 @@ private:
     pt* h_windows = nullptr;
     cudaEvent_t ev_acc0 = nullptr, ev_acc1 = nullptr, ev_t[4] = {nullptr, nullptr, nullptr, nullptr};
     bool enqueued = false;
+    // fixed-slot digits + radix sort instead of the counting sort: dense scalars over a table, and enough entries that the
+    // counting sort's scattered stores no longer stay in L2 (measured: 27 M entries 0.48 ms counting / 0.87 ms radix,
+    // 201 M entries 8.0 ms / 6.0 ms)
+    bool dense() const { return cfg.table && !cfg.sparse && cap_n * size_t(Wd) > dense_min(); }
+    static size_t dense_min() {
+        static size_t v = [] { const char* e = std::getenv("G16_DENSE_MIN"); return e ? size_t(std::atoll(e)) : size_t(80) << 20; }();
+        return v;
+    }
 };
 
 #ifdef G16_MSM_INSTANTIATE
@@ -785,6 +846,16 @@ void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     ncut_max = uint32_t(std::min<size_t>(nb, q));
     size_t e = m_max ? m_max : 1;
     vals.alloc(e * 4);
+    size_t t1 = 0;
+    if (dense()) {
+        if (m_max > size_t(INT_MAX)) throw std::runtime_error("MSM too large for the radix sort's int item count; shard it");
+        keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_b.alloc(e * 4);
+        cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
+        cub::DoubleBuffer<uint32_t> dv(vals.as<uint32_t>(), vals_b.as<uint32_t>());
+        int bits = 1;
+        while ((size_t(1) << bits) <= nb) bits++;      // keys 0 .. nb (nb = sentinel)
+        cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)e, 0, bits);
+    }
     count.alloc(size_t(nb + 1) * 4); start.alloc(size_t(nb + 1) * 4);
     ntasks.alloc(size_t(nb + 1) * 4); nparts.alloc(size_t(nb + 1) * 4); nblk.alloc(size_t(nb + 1) * 4);
     task_base.alloc(size_t(nb + 1) * 4); part_base.alloc(size_t(nb + 1) * 4); blk_base.alloc(size_t(nb + 1) * 4);
@@ -807,7 +878,7 @@ void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     params.alloc(sizeof(MsmParams));
     size_t t3 = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, t3, count.as<uint32_t>(), start.as<uint32_t>(), (int)(nb + 1));
-    cub_tmp.alloc(t3 + 256);
+    cub_tmp.alloc((t1 > t3 ? t1 : t3) + 256);
     if (!h_params) G16_CUDA(cudaMallocHost(&h_params, sizeof(MsmParams)));
     if (!h_windows) G16_CUDA(cudaMallocHost(&h_windows, 256 * sizeof(pt)));
     if (!ev_acc0) G16_CUDA(cudaEventCreate(&ev_acc0));
@@ -831,7 +902,7 @@ size_t Msm<C>::build_table(const aff* bases_, size_t n_, cudaStream_t s) {
 
 template <class C>
 void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t* inf_mask, size_t n_, cudaStream_t s,
-                     cudaStream_t s_acc, cudaEvent_t gate) {
+                     cudaStream_t s_acc, cudaEvent_t gate, cudaStream_t s_red) {
     if (n_ > cap_n) throw std::runtime_error("MSM: n exceeds reserved capacity");
     if (cfg.table && n_ != table_n) throw std::runtime_error("MSM: window table was built for a different base count");
     bases = cfg.table && n_ ? table.template as<aff>() : bases_;
@@ -844,6 +915,31 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
     // warp-aggregated counters unless the scalars are known to be dense and uniform (the H MSM over its window table)
     const bool agg = !(cfg.table && !cfg.sparse);
     G16_CUDA(cudaEventRecord(ev_t[0], s));
+    const uint32_t* entry_vals = vals.as<uint32_t>();
+    size_t tb = cub_tmp.bytes;
+    if (dense()) {
+        // ---- fixed-slot digits + radix sort (see msm_digits_dense_kernel)
+        size_t slots_n = n * size_t(Wd);
+        uint32_t m_live = 0;
+        if (n) {
+            msm_digits_dense_kernel<<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, nb, keys_a.as<uint32_t>(), vals.as<uint32_t>());
+            G16_LAUNCHED(1);
+            cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
+            cub::DoubleBuffer<uint32_t> dv(vals.as<uint32_t>(), vals_b.as<uint32_t>());
+            int bits = 1;
+            while ((size_t(1) << bits) <= nb) bits++;
+            G16_CUDA(cudaEventRecord(ev_t[1], s));
+            G16_CUDA(cub::DeviceRadixSort::SortPairs(cub_tmp.p, tb, dk, dv, (int)slots_n, 0, bits, s));
+            entry_vals = dv.Current();
+            m_live = (uint32_t)slots_n;
+            msm_lower_bound_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(dk.Current(), m_live, nb, st);
+            G16_LAUNCHED(1);
+        } else {
+            G16_CUDA(cudaMemsetAsync(st, 0, size_t(nb + 1) * 4, s));
+            G16_CUDA(cudaEventRecord(ev_t[1], s));
+        }
+        msm_plan_kernel<<<1, 1, 0, s>>>(st, nb, (uint32_t)slots, T_MIN, cfg.T, prm);
+    } else {
     // ---- counting sort of the digits by bucket
     G16_CUDA(cudaMemsetAsync(cnt, 0, size_t(nb + 1) * 4, s));
     if (n) {
@@ -851,7 +947,7 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
         else msm_digits_kernel<false, false><<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, fold, cnt, nullptr, nullptr);
         G16_LAUNCHED(1);
     }
-    size_t tb = cub_tmp.bytes;
+    tb = cub_tmp.bytes;
     G16_CUDA(cub::DeviceScan::ExclusiveSum(cub_tmp.p, tb, cnt, st, (int)(nb + 1), s));
     msm_plan_kernel<<<1, 1, 0, s>>>(st, nb, (uint32_t)slots, T_MIN, cfg.T, prm);
     G16_CUDA(cudaEventRecord(ev_t[1], s));
@@ -861,6 +957,7 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
         else msm_digits_kernel<true, false><<<dgrid, 256, 0, s>>>(scalars, (uint32_t)n, inf_mask, c, Wd, fold, cnt, st, vals.as<uint32_t>());
         G16_LAUNCHED(1);
     }
+    }   // counting sort
     // ---- tasks, longest first
     msm_count_tasks_kernel<<<(nb + 1 + 255) / 256, 256, 0, s>>>(st, nb, prm, ntasks.as<uint32_t>(), nparts.as<uint32_t>(),
                                                                 nblk.as<uint32_t>(), cut_list.as<uint32_t>());
@@ -893,26 +990,32 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
     const unsigned agrid = (nt_max + 127) / 128;
     bool launched = false;
     if constexpr (sizeof(pt) > 128) {
-        // G2: one task per lane pair (G16_G2_PAIR=0 selects the one-thread kernel for comparison)
-        static const bool pair = [] { const char* e = std::getenv("G16_G2_PAIR"); return !e || std::atoi(e) != 0; }();
+        // G2: G16_G2_PAIR=1 selects the lane-pair kernel.  Measured alone it is slower than the one-thread kernel (1.45 against
+        // 1.33 ms at 2^21, 4.92 against 4.25 ms at 2^24: 36 products per addition against Karatsuba's 28 outweigh the
+        // occupancy gained), so it stays an option
+        static const bool pair = [] { const char* e = std::getenv("G16_G2_PAIR"); return e && std::atoi(e) != 0; }();
         if (pair) {
             msm_accumulate_g2_pair_kernel<<<(2 * nt_max + 127) / 128, 128, 0, s>>>(
-                bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm,
+                bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(), t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm,
                 buckets.as<pt>(), parts.as<pt>());
             launched = true;
         }
     }
     if constexpr (sizeof(pt) <= 128) {
         if (acc_minb() == 4) {
-            msm_accumulate_kernel<C, 4><<<agrid, 128, 0, s>>>(bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(),
+            msm_accumulate_kernel<C, 4><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
                                                               t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
             launched = true;
         }
     }
     if (!launched)
-        msm_accumulate_kernel<C, 1><<<agrid, 128, 0, s>>>(bases, vals.as<uint32_t>(), order.as<uint32_t>(), t_begin.as<uint32_t>(),
+        msm_accumulate_kernel<C, 1><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
                                                           t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
     G16_CUDA(cudaEventRecord(ev_acc1, s));
+    if (s_red && s_red != s) {
+        G16_CUDA(cudaStreamWaitEvent(s_red, ev_acc1, 0));
+        s = s_red;
+    }
     const unsigned cgrid = (unsigned)std::min<size_t>((size_t(ncut_max) + 127) / 128, size_t(sms) * 4);
     msm_combine_small_kernel<C><<<cgrid ? cgrid : 1, 128, 0, s>>>(cut_list.as<uint32_t>(), prm, part_base.as<uint32_t>(), parts.as<pt>(),
                                                                   buckets.as<pt>());

@@ -10,8 +10,8 @@
 // transform runs decimation-in-time (bit-reversed in, natural out) -- no bit-reversal pass exists.
 //
 // A transform of 2^logn points is ceil(logn/10) passes; a pass stages up to 10 butterfly levels of a 1024-element
-// tile in shared memory and makes one coalesced round trip to HBM.  Index math prototyped in scratch/nttsim.py
-// (fused twiddles) and scratch/nttsim2.py (split twiddles, the version that runs) against the oracle.
+// tile in shared memory and makes one coalesced round trip to HBM.  Index math prototyped in tools/nttsim.py
+// (fused twiddles) and tools/nttsim2.py (split twiddles, the version that runs) against the oracle.
 #pragma once
 #include <cstdlib>
 #include <vector>
@@ -111,7 +111,7 @@ ntt_pass_fused_kernel(fe_t* __restrict__ a, int logn, int s_lo, int k, const fe_
 // applied while storing (DIF) or loading (DIT); passes with s_lo == 0 have none.  Against the fused version: the
 // per-butterfly table load from L2 becomes a shared-memory read, a butterfly whose sub-transform twiddle is 1
 // (tl == 0; whole warps, see the thread mapping) skips its product -- 28 % of a 2^7 pass -- and the inverse
-// pass negates its table once instead of per butterfly.  Index math prototyped in scratch/nttsim2.py.
+// pass negates its table once instead of per butterfly.  Index math prototyped in tools/nttsim2.py.
 // Shared layout: element (t, qi) of the tile at slot t * S + qi, two planes of 16-byte halves (a 32-byte element
 // per lane would make every access a 2-way bank conflict), one slot of padding per 8.
 constexpr int NTT_PLANE = NTT_TILE + NTT_TILE / 8;

@@ -172,6 +172,7 @@ struct g16_zkey {
     DevBuf w;                  // witness, n_vars x 32 B standard form
     DevBuf w_next;             // the witness of the NEXT proof, filled by g16_witness_prefetch while this one is proved
     cudaStream_t s_copy = nullptr;
+    cudaStream_t s_hpre = nullptr;     // H preparation in the chained schedule
     cudaEvent_t ev_copy = nullptr;
     bool next_ready = false;
     std::vector<uint8_t> next_public;
@@ -194,6 +195,7 @@ struct g16_zkey {
         cudaSetDevice(device);
         if (s_main) cudaStreamDestroy(s_main);
         if (s_copy) cudaStreamDestroy(s_copy);
+        if (s_hpre) cudaStreamDestroy(s_hpre);
         if (ev_copy) cudaEventDestroy(ev_copy);
         for (auto& s : s_pre)
             if (s) cudaStreamDestroy(s);
@@ -314,14 +316,18 @@ static g16_zkey* zkey_build(const uint8_t* data, size_t len, const g16_opts* opt
     int prio_lo = 0, prio_hi = 0;
     G16_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     int prio_mid = prio_hi < prio_lo - 1 ? prio_hi + 1 : prio_hi;
-    G16_CUDA(cudaStreamCreateWithPriority(&zk->s_main, cudaStreamNonBlocking, prio_hi));
+    static const bool chain_main = [] { const char* e = std::getenv("G16_CHAIN"); return e && std::atoi(e) != 0; }();
+    G16_CUDA(cudaStreamCreateWithPriority(&zk->s_main, cudaStreamNonBlocking, chain_main ? prio_hi + 1 : prio_hi));
     // G16_HPRIO (scheduling experiment): priority of the H accumulation stream, 0 = lowest (default), 1 = middle, 2 = highest
     static const int hprio = [] { const char* e = std::getenv("G16_HPRIO"); return e ? std::atoi(e) : 0; }();
     int prio_h = hprio == 2 ? prio_hi : hprio == 1 ? prio_mid : prio_lo;
     // with the H accumulation above them, the witness accumulations drop to the lowest priority (they become the filler)
     int prio_w = hprio == 2 ? prio_lo : prio_mid;
+    static const bool chain = [] { const char* e = std::getenv("G16_CHAIN"); return e && std::atoi(e) != 0; }();
+    if (chain) prio_h = prio_w = prio_hi;   // the side streams only carry latency-bound work then
     for (int i = 0; i < 5; i++)
         G16_CUDA(cudaStreamCreateWithPriority(&zk->s_msm[i], cudaStreamNonBlocking, i == 4 ? prio_h : prio_w));
+    G16_CUDA(cudaStreamCreateWithPriority(&zk->s_hpre, cudaStreamNonBlocking, prio_hi));
     // digits + sort of the witness MSMs are HBM-bound and short; at the transforms' priority they interleave with the
     // (integer-bound) transforms instead of being starved by them, so the accumulations are ready when the transforms end
     for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamCreateWithPriority(&zk->s_pre[i], cudaStreamNonBlocking, prio_hi));
@@ -560,6 +566,11 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
     G16_CUDA(cudaSetDevice(zk->device));
     auto t0 = std::chrono::steady_clock::now();
     const uint32_t* w = zk->w.as<uint32_t>();
+    // G16_SERIAL=1 (measurement): every kernel of the proof on ONE stream, i.e. the sum of the stand-alone phase times
+    static const bool serial = [] { const char* e = std::getenv("G16_SERIAL"); return e && std::atoi(e) != 0; }();
+    cudaStream_t s_pre[4], s_msm[5];
+    for (int i = 0; i < 4; i++) s_pre[i] = serial ? zk->s_main : zk->s_pre[i];
+    for (int i = 0; i < 5; i++) s_msm[i] = serial ? zk->s_main : zk->s_msm[i];
     try {
         G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
         // witness-scalar MSMs start at once; the H MSM waits for the NTT pipeline.  Preparation (counting sort of the
@@ -567,29 +578,44 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         // integer-bound transforms; accumulations + reductions at middle priority.  B2 first: its G2 reductions are the
         // longest latency-bound tail.
         for (int i = 0; i < 4; i++) {
-            G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], zk->ev[0], 0));
-            G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], zk->s_pre[i]));
+            G16_CUDA(cudaStreamWaitEvent(s_pre[i], zk->ev[0], 0));
+            G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], s_pre[i]));
         }
         // G16_GATE (scheduling experiment): bit 0 = the G1 witness accumulations wait for the transforms, bit 1 = B2 too.
         // The transforms then run without long-lived accumulation CTAs in their way, at the price of idle pipe slots.
         static const int gate_mask = [] { const char* e = std::getenv("G16_GATE"); return e ? std::atoi(e) : 0; }();
         const bool deferred = (gate_mask & 4) != 0;   // bit 2: enqueue the witness MSMs after the H chain
         cudaEvent_t ntt_done = zk->ev[2];
+        // G16_CHAIN=1 (scheduling experiment): the pipe-bound kernels (transforms, then the five accumulations) back to
+        // back on the transform stream; preparation and reductions (latency-bound) on the side streams
+        static const bool chain = [] { const char* e = std::getenv("G16_CHAIN"); return e && std::atoi(e) != 0; }();
         auto witness_msms = [&]() {
+        if (chain) {
+            zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, s_pre[2], zk->s_main, nullptr, s_msm[2]);
+            G16_CUDA(cudaEventRecord(zk->ev[8], s_msm[2]));
+            zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, s_pre[0], zk->s_main, nullptr, s_msm[0]);
+            G16_CUDA(cudaEventRecord(zk->ev[4], s_msm[0]));
+            zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, s_pre[1], zk->s_main, nullptr, s_msm[1]);
+            G16_CUDA(cudaEventRecord(zk->ev[6], s_msm[1]));
+            zk->C.msm.enqueue(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8, zk->C.mask.as<uint32_t>(), zk->C.n,
+                              s_pre[3], zk->s_main, nullptr, s_msm[3]);
+            G16_CUDA(cudaEventRecord(zk->ev[10], s_msm[3]));
+            return;
+        }
         if ((gate_mask & 8) && !deferred)   // bit 3: the witness MSMs' preparation waits for the transforms as well
-            for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(zk->s_pre[i], ntt_done, 0));
-        zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, zk->s_pre[2], zk->s_msm[2],
+            for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(s_pre[i], ntt_done, 0));
+        zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, s_pre[2], s_msm[2],
                            (gate_mask & 2) && !deferred ? ntt_done : nullptr);
-        G16_CUDA(cudaEventRecord(zk->ev[8], zk->s_msm[2]));
-        zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, zk->s_pre[0], zk->s_msm[0],
+        G16_CUDA(cudaEventRecord(zk->ev[8], s_msm[2]));
+        zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, s_pre[0], s_msm[0],
                           (gate_mask & 1) && !deferred ? ntt_done : nullptr);
-        G16_CUDA(cudaEventRecord(zk->ev[4], zk->s_msm[0]));
-        zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, zk->s_pre[1], zk->s_msm[1],
+        G16_CUDA(cudaEventRecord(zk->ev[4], s_msm[0]));
+        zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, s_pre[1], s_msm[1],
                            (gate_mask & 1) && !deferred ? ntt_done : nullptr);
-        G16_CUDA(cudaEventRecord(zk->ev[6], zk->s_msm[1]));
+        G16_CUDA(cudaEventRecord(zk->ev[6], s_msm[1]));
         zk->C.msm.enqueue(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8, zk->C.mask.as<uint32_t>(), zk->C.n,
-                          zk->s_pre[3], zk->s_msm[3], (gate_mask & 1) && !deferred ? ntt_done : nullptr);
-        G16_CUDA(cudaEventRecord(zk->ev[10], zk->s_msm[3]));
+                          s_pre[3], s_msm[3], (gate_mask & 1) && !deferred ? ntt_done : nullptr);
+        G16_CUDA(cudaEventRecord(zk->ev[10], s_msm[3]));
         };
         if (js) {
             G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
@@ -607,9 +633,15 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         // H: preparation stays on the transform stream (highest priority, already ordered after the join); only the
         // accumulation and reductions move to the lowest-priority stream, filling the machine under everything else
         G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
+        if (chain) {
+            // H preparation on a side stream once the join is done; its accumulation last on the main stream
+            G16_CUDA(cudaStreamWaitEvent(zk->s_hpre, zk->ev[2], 0));   // the join, not the accumulations queued behind it
+            zk->H.msm.enqueue(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
+                              zk->s_hpre, zk->s_main, nullptr, s_msm[4]);
+        } else
         zk->H.msm.enqueue(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
-                          zk->s_main, zk->s_msm[4]);
-        G16_CUDA(cudaEventRecord(zk->ev[12], zk->s_msm[4]));
+                          zk->s_main, s_msm[4]);
+        G16_CUDA(cudaEventRecord(zk->ev[12], s_msm[4]));
         if (deferred) witness_msms();
         // results, in the order they are expected to finish; each finished MSM's Horner chain (255 doublings on the
         // host) overlaps the MSMs still running
@@ -618,7 +650,7 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         zk->C.msm.wait();  zk->fin_c = zk->C.msm.finish<HG1>();
         zk->B2.msm.wait(); zk->fin_b2 = zk->B2.msm.finish<HG2>();
         zk->H.msm.wait();
-        for (int i = 0; i < 5; i++) G16_CUDA(cudaStreamSynchronize(zk->s_msm[i]));
+        for (int i = 0; i < 5; i++) G16_CUDA(cudaStreamSynchronize(s_msm[i]));
         G16_CUDA(cudaStreamSynchronize(zk->s_main));
     } catch (...) {
         // a failed enqueue leaves kernels of this proof in flight on other streams: drain them before the handle is

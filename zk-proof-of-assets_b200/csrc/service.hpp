@@ -98,7 +98,8 @@ struct Mapped {
 
 // write to a temporary beside the target, then rename: a reader never sees a half-written proof
 inline bool write_file(const std::string& path, const char* data, size_t n, std::string& err) {
-    std::string tmp = path + ".tmp." + std::to_string(::getpid());
+    static std::atomic<unsigned long> seq{0};   // handler threads of one service process share the pid
+    std::string tmp = path + ".tmp." + std::to_string(::getpid()) + "." + std::to_string(seq++);
     FILE* f = std::fopen(tmp.c_str(), "wb");
     if (!f) { err = "cannot create " + tmp + ": " + std::strerror(errno); return false; }
     bool ok = std::fwrite(data, 1, n, f) == n;

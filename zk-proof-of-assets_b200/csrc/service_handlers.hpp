@@ -53,15 +53,25 @@ inline std::string Server::prove(const std::vector<std::string>& f) {
     uint32_t nv = 0, npub = 0, dom = 0;
     uint64_t nc = 0;
     g16_zkey_info(r->zk, &nv, &npub, &dom, &nc);
-    std::vector<char> proof(4096), pub(256 + 80 * size_t(npub));
+    // snarkjs style costs up to 82 bytes per public signal (newline, indent, quotes, 77 digits, comma)
+    std::vector<char> proof(4096), pub(256 + 96 * size_t(npub));
     size_t pl = proof.size(), ul = pub.size();
     auto tp = std::chrono::steady_clock::now();
     int rc = g16_prove(r->zk, wtns.p, wtns.n, proof.data(), &pl, pub.data(), &ul, &o);
+    if (rc == G16_ERR_SHORT_BUFFER) {   // the required sizes were written back: resize and finish (witness is loaded)
+        proof.resize(pl + 1);
+        pub.resize(ul + 1);
+        pl = proof.size();
+        ul = pub.size();
+        rc = g16_prove_loaded(r->zk, proof.data(), &pl, pub.data(), &ul, &o);
+    }
     double prove_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tp).count();
     std::string msg = rc == G16_OK ? "" : g16_last_error();
     int device = r->device;
     r->proofs++;
-    release(r, false);   // a failed proof (bad witness) leaves the key resident and usable
+    // a failed proof (bad witness) leaves the key resident and usable; after a CUDA-class error the handle's device
+    // state is not trusted any more and the resident copy is dropped
+    release(r, rc == G16_ERR_CUDA);
     if (rc != G16_OK) {
         n_errors_++;
         return err_reply(rc, msg);

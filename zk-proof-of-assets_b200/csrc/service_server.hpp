@@ -38,6 +38,7 @@ public:
             std::fprintf(stderr, "prover: cannot listen on %s: %s\n", sock_.c_str(), std::strerror(errno));
             return 1;
         }
+        ::chmod(sock_.c_str(), 0600);   // requests name arbitrary output paths and can shut the service down: owner only
         std::fprintf(stderr, "prover: %s serving on %s, %zu device(s), %d key(s) per device\n", g16_version(),
                      sock_.c_str(), devices_.size(), max_keys_);
         while (!stop_.load()) {
@@ -53,11 +54,13 @@ public:
                 active_--;
             }).detach();
         }
-        for (int i = 0; i < 3000 && active_.load() > 0; i++) std::this_thread::sleep_for(std::chrono::milliseconds(10));
         ::unlink(sock_.c_str());
+        // wait for the handlers that are still proving or opening a key (a large proof can take a while); a handle
+        // that is still busy after that is left to process exit rather than freed under a running proof
+        for (int i = 0; i < 60000 && active_.load() > 0; i++) std::this_thread::sleep_for(std::chrono::milliseconds(10));
         std::lock_guard<std::mutex> g(mu_);
         for (auto& r : table_)
-            if (r->zk) g16_zkey_close(r->zk);
+            if (r->zk && !r->busy) g16_zkey_close(r->zk);
         table_.clear();
         return 0;
     }
@@ -98,7 +101,10 @@ private:
             for (size_t i = 0; i < devices_.size(); i++)
                 if (!holds[i] && (best < 0 || count[i] < count[best])) best = int(i);
             if (best >= 0) {
-                evict_for(devices_[best]);
+                if (!evict_for(devices_[best])) {   // the device is full of busy keys: wait for one to be released
+                    cv_.wait(lk);
+                    continue;
+                }
                 auto r = std::make_shared<Resident>();
                 r->key = key;
                 r->device = devices_[best];
@@ -126,7 +132,8 @@ private:
     }
 
     // called with mu_ held: keep at most max_keys_ - 1 other copies on `device`, idle least-recently-used first
-    void evict_for(int device) {
+    // makes room for one more key on `device`; false = every resident key there is busy and the device is at --max-keys
+    bool evict_for(int device) {
         for (;;) {
             int n = 0;
             std::shared_ptr<Resident> lru;
@@ -135,7 +142,8 @@ private:
                     n++;
                     if (!r->busy && (!lru || r->last_used < lru->last_used)) lru = r;
                 }
-            if (n < max_keys_ || !lru) return;
+            if (n < max_keys_) return true;
+            if (!lru) return false;
             if (lru->zk) g16_zkey_close(lru->zk);
             table_.remove(lru);
         }
