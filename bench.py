@@ -32,6 +32,7 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # before torch creates the CUDA context (see csrc/prover.cu)
 
 # name -> (n_vars, n_public, n_constraints, description); sizes from SURVEY.md section 6a / 8(d)
 WORKLOADS = {

@@ -90,6 +90,11 @@ int g16_prove_partial(g16_zkey* zk, uint8_t* partial_out);
 int g16_prove_combine(g16_zkey* zk, const uint8_t* partials, int count, char* proof_json, size_t* proof_len,
                       char* public_json, size_t* public_len, const g16_opts* opts);
 
+/* Start the four witness-scalar MSMs (A, B1, B2, C) of the loaded witness now and return without waiting.  The next
+ * g16_prove_partial / g16_prove_partial_joined / g16_prove_loaded on this handle picks them up instead of starting its
+ * own.  A sharded proof calls this before its transforms and the exchange of polynomial slices, which those MSMs do
+ * not depend on, so that they run underneath both. */
+int g16_prove_begin(g16_zkey* zk);
 /* Transforms spread over the ranks (SURVEY.md 8(e) task placement): with G >= 2 ranks the three coset transforms
  * (rows a5-a7 for A, B, C) need not be repeated on every rank.  Rank o runs g16_h_transform(zk, mask of the
  * polynomials it owns: 1 = A, 2 = B, 4 = C): R1CS evaluation (row a4, cheap, every rank) + the odd-coset transform of

@@ -21,6 +21,10 @@ import ctypes
 import json
 import os
 
+# one hardware queue per stream of a proof (see csrc/prover.cu); must be in the environment before the process creates
+# its CUDA context, e.g. before torch touches the device
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libg16b200.so")
 SYNTH_LIB_PATH = os.path.join(_HERE, "libg16synth.so")
@@ -37,7 +41,7 @@ ABI_SYMBOLS = [
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
     "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace", "g16_h_transform", "g16_h_buffer",
-    "g16_prove_partial_joined", "g16_verify", "g16_sanitize",
+    "g16_prove_partial_joined", "g16_prove_begin", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
     "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files",
 ]
@@ -117,6 +121,7 @@ def lib():
         L.g16_h_transform.argtypes = [ctypes.c_void_p, ctypes.c_int]
         L.g16_h_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_prove_partial_joined.argtypes = [ctypes.c_void_p] * 5
+        L.g16_prove_begin.argtypes = [ctypes.c_void_p]
         L.g16_sanitize.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
                                    ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_verify.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
@@ -277,6 +282,10 @@ class ZKey:
         out = ctypes.create_string_buffer(PARTIAL_BYTES)
         _check(lib().g16_prove_partial(self._h, out))
         return out.raw
+
+    def prove_begin(self):
+        """start the witness-scalar MSMs of the loaded witness now (asynchronous); the next prove_partial* picks them up"""
+        _check(lib().g16_prove_begin(self._h))
 
     def h_transform(self, which):
         """rows a4-a7 for the polynomials in bit mask `which` (1 A, 2 B, 4 C); results stay in the device buffers"""
@@ -700,6 +709,7 @@ def prove_sharded_distributed(zk, wtns=None, r=None, s=None, style=STYLE_RAPIDSN
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     if wtns is not None:
         zk.load_witness(wtns)
+    zk.prove_begin()      # the witness MSMs depend on neither the transforms nor the exchange: they run underneath both
     mask = sum(1 << p for p in range(3) if transform_owner(p, world) == rank)
     zk.h_transform(mask)
     a, b, c = exchange_h_slices(zk, group)

@@ -29,6 +29,13 @@ using namespace g16h;
 
 namespace g16 {
 
+// A proof is spread over a dozen streams (transforms, five MSMs x preparation / accumulation).  CUDA maps streams onto
+// CUDA_DEVICE_MAX_CONNECTIONS hardware queues (default 8); streams that share a queue pick up false dependencies on each
+// other (measured: the H preparation waited 5 ms behind another stream's accumulations, 14.6 -> 13.9 ms per proof at
+// 2^21 once every stream has its own queue).  The variable is read when the CUDA context is created, so it is set when
+// the library is loaded, without overriding the user's choice.
+static const int g_max_connections_set = [] { return ::setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }();
+
 thread_local std::string g_last_error;
 
 int fail(int code, const std::string& msg) {
@@ -190,6 +197,7 @@ struct g16_zkey {
     double t_ms[10] = {0};
     double t_horner_ms = 0;
     bool partial_done = false;
+    bool witness_enqueued = false;   // g16_prove_begin ran: the witness MSMs of this proof are already in flight
 
     ~g16_zkey() {
         cudaSetDevice(device);
@@ -530,6 +538,7 @@ static void witness_load(g16_zkey* zk, const uint8_t* data, size_t len) {
     zk->t_ms[0] = ms;
     zk->witness_loaded = true;
     zk->partial_done = false;
+    zk->witness_enqueued = false;
 }
 
 // rows a4-a8 on s_main: leaves the H scalars (standard form) in zk->pa
@@ -561,7 +570,7 @@ struct JoinedSlices {
 // The whole proof is ONE enqueue: no host thread and no read-back of a counter sits between the kernels (the MSMs size
 // their launches from device memory, msm.cuh); the host only waits for the five results at the end, in the order they
 // finish, and runs each finished MSM's window Horner chain while the others still compute.
-static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
+static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr, bool only_witness = false) {
     if (!zk->witness_loaded) throw std::runtime_error("no witness loaded");
     G16_CUDA(cudaSetDevice(zk->device));
     auto t0 = std::chrono::steady_clock::now();
@@ -572,20 +581,22 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
     for (int i = 0; i < 4; i++) s_pre[i] = serial ? zk->s_main : zk->s_pre[i];
     for (int i = 0; i < 5; i++) s_msm[i] = serial ? zk->s_main : zk->s_msm[i];
     try {
-        G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
+        if (!zk->witness_enqueued) G16_CUDA(cudaEventRecord(zk->ev[0], zk->s_main));
         // witness-scalar MSMs start at once; the H MSM waits for the NTT pipeline.  Preparation (counting sort of the
         // digits, HBM-bound and short) on streams of the transforms' priority so that it interleaves with the
         // integer-bound transforms; accumulations + reductions at middle priority.  B2 first: its G2 reductions are the
         // longest latency-bound tail.
-        for (int i = 0; i < 4; i++) {
-            G16_CUDA(cudaStreamWaitEvent(s_pre[i], zk->ev[0], 0));
-            G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], s_pre[i]));
-        }
+        if (!zk->witness_enqueued)
+            for (int i = 0; i < 4; i++) {
+                G16_CUDA(cudaStreamWaitEvent(s_pre[i], zk->ev[0], 0));
+                G16_CUDA(cudaEventRecord(zk->ev[3 + 2 * i], s_pre[i]));
+            }
         // G16_GATE (scheduling experiment): bit 0 = the G1 witness accumulations wait for the transforms, bit 1 = B2 too.
         // The transforms then run without long-lived accumulation CTAs in their way, at the price of idle pipe slots.
         static const int gate_mask = [] { const char* e = std::getenv("G16_GATE"); return e ? std::atoi(e) : 0; }();
         const bool deferred = (gate_mask & 4) != 0;   // bit 2: enqueue the witness MSMs after the H chain
         cudaEvent_t ntt_done = zk->ev[2];
+        const bool nogate = deferred || only_witness;   // nothing to wait for when the transforms are not part of this enqueue
         // G16_CHAIN=1 (scheduling experiment): the pipe-bound kernels (transforms, then the five accumulations) back to
         // back on the transform stream; preparation and reductions (latency-bound) on the side streams
         static const bool chain = [] { const char* e = std::getenv("G16_CHAIN"); return e && std::atoi(e) != 0; }();
@@ -602,22 +613,24 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
             G16_CUDA(cudaEventRecord(zk->ev[10], s_msm[3]));
             return;
         }
-        if ((gate_mask & 8) && !deferred)   // bit 3: the witness MSMs' preparation waits for the transforms as well
+        if ((gate_mask & 8) && !nogate)   // bit 3: the witness MSMs' preparation waits for the transforms as well
             for (int i = 0; i < 4; i++) G16_CUDA(cudaStreamWaitEvent(s_pre[i], ntt_done, 0));
         zk->B2.msm.enqueue(zk->B2.bases.as<g2_aff>(), w + zk->B2.lo * 8, zk->B2.mask.as<uint32_t>(), zk->B2.n, s_pre[2], s_msm[2],
-                           (gate_mask & 2) && !deferred ? ntt_done : nullptr);
+                           (gate_mask & 2) && !nogate ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[8], s_msm[2]));
         zk->A.msm.enqueue(zk->A.bases.as<g1_aff>(), w + zk->A.lo * 8, zk->A.mask.as<uint32_t>(), zk->A.n, s_pre[0], s_msm[0],
-                          (gate_mask & 1) && !deferred ? ntt_done : nullptr);
+                          (gate_mask & 1) && !nogate ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[4], s_msm[0]));
         zk->B1.msm.enqueue(zk->B1.bases.as<g1_aff>(), w + zk->B1.lo * 8, zk->B1.mask.as<uint32_t>(), zk->B1.n, s_pre[1], s_msm[1],
-                           (gate_mask & 1) && !deferred ? ntt_done : nullptr);
+                           (gate_mask & 1) && !nogate ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[6], s_msm[1]));
         zk->C.msm.enqueue(zk->C.bases.as<g1_aff>(), w + (size_t(zk->n_public) + 1 + zk->C.lo) * 8, zk->C.mask.as<uint32_t>(), zk->C.n,
-                          s_pre[3], s_msm[3], (gate_mask & 1) && !deferred ? ntt_done : nullptr);
+                          s_pre[3], s_msm[3], (gate_mask & 1) && !nogate ? ntt_done : nullptr);
         G16_CUDA(cudaEventRecord(zk->ev[10], s_msm[3]));
         };
-        if (js) {
+        if (only_witness) {
+            // fall through to the witness MSMs below
+        } else if (js) {
             G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
             if (zk->H.n) {
                 ntt_join_kernel<<<(unsigned)((zk->H.n + 255) / 256), 256, 0, zk->s_main>>>(
@@ -629,7 +642,12 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         } else {
             enqueue_h_pipeline(zk);
         }
-        if (!deferred) witness_msms();   // after the transforms are enqueued: ev[2] is this proof's record
+        if (only_witness) {   // g16_prove_begin: the witness MSMs only, nothing waited for
+            witness_msms();
+            zk->witness_enqueued = true;
+            return;
+        }
+        if (!deferred && !zk->witness_enqueued) witness_msms();   // after the transforms are enqueued: ev[2] is this proof's record
         // H: preparation stays on the transform stream (highest priority, already ordered after the join); only the
         // accumulation and reductions move to the lowest-priority stream, filling the machine under everything else
         G16_CUDA(cudaEventRecord(zk->ev[11], zk->s_main));
@@ -642,7 +660,8 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         zk->H.msm.enqueue(zk->H.bases.as<g1_aff>(), zk->pa.as<uint32_t>() + zk->H.lo * 8, zk->H.mask.as<uint32_t>(), zk->H.n,
                           zk->s_main, s_msm[4]);
         G16_CUDA(cudaEventRecord(zk->ev[12], s_msm[4]));
-        if (deferred) witness_msms();
+        if (deferred && !zk->witness_enqueued) witness_msms();
+        zk->witness_enqueued = false;
         // results, in the order they are expected to finish; each finished MSM's Horner chain (255 doublings on the
         // host) overlaps the MSMs still running
         zk->A.msm.wait();  zk->fin_a = zk->A.msm.finish<HG1>();
@@ -657,6 +676,7 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr) {
         // reused (the service keeps a key resident after a failed proof), and forget the half-made results
         cudaDeviceSynchronize();
         zk->partial_done = false;
+        zk->witness_enqueued = false;
         throw;
     }
     float ms = 0;
@@ -940,6 +960,15 @@ int g16_prove_partial(g16_zkey* zk, uint8_t* partial_out) {
         if (!zk || !partial_out) return fail(G16_ERR_GENERIC, "null argument");
         prove_device(zk);
         export_partial(zk, partial_out);
+        return (int)G16_OK;
+    });
+}
+
+int g16_prove_begin(g16_zkey* zk) {
+    return guarded([&]() {
+        if (!zk) return fail(G16_ERR_GENERIC, "null handle");
+        if (zk->witness_enqueued) return (int)G16_OK;
+        prove_device(zk, nullptr, true);
         return (int)G16_OK;
     });
 }
