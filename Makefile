@@ -4,7 +4,7 @@ CSRC     := $(PKG)/csrc
 NVCC     ?= nvcc
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
-OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o $(CSRC)/poseidon.o $(CSRC)/verify.o $(CSRC)/merkle.o
+OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o $(CSRC)/poseidon.o $(CSRC)/verify.o $(CSRC)/merkle.o $(CSRC)/setup.o
 HDRS     := $(wildcard $(CSRC)/*.cuh) $(filter-out $(CSRC)/service% $(CSRC)/verify%,$(wildcard $(CSRC)/*.hpp)) include/g16_b200.h
 
 all: $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover
@@ -16,6 +16,9 @@ $(CSRC)/verify.o: $(CSRC)/verify.cpp $(wildcard $(CSRC)/verify*.hpp) $(CSRC)/hos
 	g++ -O2 -std=c++17 -fPIC -Wall -Iinclude -c $< -o $@
 
 $(CSRC)/merkle.o: $(CSRC)/merkle.cpp $(wildcard $(CSRC)/verify*.hpp) $(CSRC)/hostfield.hpp include/g16_b200.h
+	g++ -O2 -std=c++17 -fPIC -Wall -Iinclude -c $< -o $@
+
+$(CSRC)/setup.o: $(CSRC)/setup.cpp $(CSRC)/setup_hash.hpp $(wildcard $(CSRC)/verify*.hpp) $(CSRC)/hostfield.hpp include/g16_b200.h
 	g++ -O2 -std=c++17 -fPIC -Wall -Iinclude -c $< -o $@
 
 $(PKG)/libg16b200.so: $(OBJS)

@@ -210,6 +210,27 @@ int g16_merkle_find(const g16_merkle* t, const uint8_t hash[32], uint64_t from, 
  * poa_input_json may be NULL (root only, empty proofs file). */
 int g16_merkle_files(const char* anon_set_csv, const char* poa_input_json, const char* output_dir, const g16_opts* opts);
 
+
+/* ---- phase-2 ceremony steps and verification-key export (file level) ----------------------
+ * What scripts/g16_setup.sh:254-295 runs through snarkjs: `zkey contribute`, `zkey beacon`, `zkey export
+ * verificationkey`.  A contribution multiplies delta by a secret delta' and sections 8 (C) and 9 (H) by 1/delta' (on
+ * the GPU: g16_batch_apply_key), copies the other sections, and appends a section-10 record in snarkjs' layout
+ * (deltaAfter, g1_s, g1_sx, g2_spx, Blake2b-512 transcript, name / beacon parameters).  The secrets and the
+ * proof-of-knowledge point are derived with this library's own Blake2b construction (oracle/setup.py is the
+ * specification); acceptance of that record by `snarkjs zkey verify` is unverified on this box (no node).
+ * entropy may be NULL (64 bytes are drawn with getrandom(2)).  contribution_hash (optional) receives the Blake2b-512
+ * hash snarkjs prints as "Contribution Hash". */
+int g16_zkey_contribute(const char* zkey_in, const char* zkey_out, const char* name, const uint8_t* entropy, size_t entropy_len,
+                        const g16_opts* opts, uint8_t contribution_hash[64]);
+/* delta' from 2^num_iterations_exp iterations of SHA-256 over beacon_hash (scripts/g16_setup.sh:272-277) */
+int g16_zkey_beacon(const char* zkey_in, const char* zkey_out, const char* name, const uint8_t* beacon_hash, size_t hash_len,
+                    uint32_t num_iterations_exp, const g16_opts* opts, uint8_t contribution_hash[64]);
+/* the text of verification_key.json (JSON.stringify(vKey, null, 1), vk_alphabeta_12 included); host only, no GPU.
+ * Returns G16_ERR_SHORT_BUFFER with the required size in *out_len when the buffer is too small. */
+int g16_zkey_export_vkey(const char* zkey_path, char* out, size_t* out_len);
+/* test hook: which = 0 Blake2b-512 (64 bytes out), 1 SHA-256 (32 bytes out) */
+int g16_test_hash(int which, const uint8_t* data, size_t n, uint8_t* out);
+
 #ifdef __cplusplus
 }
 #endif

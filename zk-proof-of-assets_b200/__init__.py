@@ -44,6 +44,7 @@ ABI_SYMBOLS = [
     "g16_prove_partial_joined", "g16_prove_begin", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
     "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files",
+    "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -136,6 +137,12 @@ def lib():
         L.g16_merkle_proof.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_merkle_find.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p]
         L.g16_merkle_files.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
+        L.g16_zkey_contribute.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
+                                          ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_beacon.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
+                                      ctypes.c_uint32, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_export_vkey.argtypes = [ctypes.c_char_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_test_hash.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
         _lib = L
     return _lib
 
@@ -559,6 +566,46 @@ def merkle_files(anon_set_csv, poa_input_json, output_dir, device=-1):
     o = make_opts(device=device)
     _check(lib().g16_merkle_files(os.fsencode(anon_set_csv), os.fsencode(poa_input_json) if poa_input_json else None,
                                   os.fsencode(output_dir), ctypes.byref(o)))
+
+
+# ---- phase-2 ceremony steps + vkey export (scripts/g16_setup.sh:254-295) ------------------------------------------
+def zkey_contribute(zkey_in, zkey_out, name="", entropy=None, device=-1):
+    """`snarkjs zkey contribute <in> <out> --name=.. -e=..`; sections 8/9 are updated on the GPU.  -> contribution hash"""
+    o = make_opts(device=device)
+    h = ctypes.create_string_buffer(64)
+    e = None if entropy is None else (entropy.encode() if isinstance(entropy, str) else bytes(entropy))
+    _check(lib().g16_zkey_contribute(os.fsencode(zkey_in), os.fsencode(zkey_out), name.encode(), e, len(e) if e else 0,
+                                     ctypes.byref(o), h))
+    return h.raw
+
+
+def zkey_beacon(zkey_in, zkey_out, beacon_hash, num_iterations_exp, name="", device=-1):
+    """`snarkjs zkey beacon <in> <out> <beaconHash hex> <numIterationsExp> -n=..`  -> contribution hash"""
+    o = make_opts(device=device)
+    h = ctypes.create_string_buffer(64)
+    b = bytes.fromhex(beacon_hash) if isinstance(beacon_hash, str) else bytes(beacon_hash)
+    _check(lib().g16_zkey_beacon(os.fsencode(zkey_in), os.fsencode(zkey_out), name.encode(), b, len(b), num_iterations_exp,
+                                 ctypes.byref(o), h))
+    return h.raw
+
+
+def zkey_export_vkey(zkey_path):
+    """`snarkjs zkey export verificationkey <zkey>` -> the text of verification_key.json (host only)"""
+    n = ctypes.c_size_t(1 << 16)
+    buf = ctypes.create_string_buffer(n.value)
+    rc = lib().g16_zkey_export_vkey(os.fsencode(zkey_path), buf, ctypes.byref(n))
+    if rc == G16_ERR_SHORT_BUFFER:
+        buf = ctypes.create_string_buffer(n.value + 1)
+        n = ctypes.c_size_t(len(buf))
+        rc = lib().g16_zkey_export_vkey(os.fsencode(zkey_path), buf, ctypes.byref(n))
+    _check(rc)
+    return buf.raw[:n.value].decode()
+
+
+def test_hash(which, data):
+    out = ctypes.create_string_buffer(64 if which == 0 else 32)
+    _check(lib().g16_test_hash(which, bytes(data), len(data), out))
+    return out.raw
 
 
 # ---- SYNTH-1 fixtures (bench/test support) ------------------------------------------------------------------

@@ -1008,6 +1008,15 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
             launched = true;
         }
     }
+    if constexpr (sizeof(pt) > 128) {
+        // G2, one thread per task: G16_G2_MINB=3 caps the kernel at 168 registers (3 CTAs per SM, more spills) instead of 255
+        static const int g2_minb = [] { const char* e = std::getenv("G16_G2_MINB"); return e ? std::atoi(e) : 1; }();
+        if (!launched && g2_minb == 3) {
+            msm_accumulate_kernel<C, 3><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
+                                                              t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
+            launched = true;
+        }
+    }
     if (!launched)
         msm_accumulate_kernel<C, 1><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
                                                           t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());

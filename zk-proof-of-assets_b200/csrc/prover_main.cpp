@@ -15,11 +15,16 @@
 //                                   the limb file scripts/sanitize_groth16_proof.py:112-123 writes, byte for byte
 // Anonymity-set Merkle tree (the argv of the reference's `merkle-tree`, scripts/merkle_tree.rs:29-44):
 //     prover --merkle-tree --anon-set <csv> --poa-input-data <json> --output-dir <dir>
+// Setup steps (snarkjs' argument order, scripts/g16_setup.sh:254-295):
+//     prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
+//     prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]
+//     prover --zkey-export-vkey <zkey> <verification_key.json>
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <vector>
 
 #include "g16_b200.h"
 #include "service_handlers.hpp"
@@ -137,8 +142,71 @@ static int merkle_cli(int argc, char** argv) {
     return 0;
 }
 
+// the setup steps of scripts/g16_setup.sh:254-295 with snarkjs' argument order:
+//   prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
+//   prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]
+//   prover --zkey-export-vkey <zkey> <verification_key.json>
+static int setup_cli(int argc, char** argv) {
+    std::string cmd = argv[1];
+    std::vector<std::string> pos;
+    std::string name, entropy;
+    bool has_entropy = false;
+    for (int i = 2; i < argc; i++) {
+        std::string a = argv[i];
+        if (a.rfind("--name=", 0) == 0) name = a.substr(7);
+        else if (a.rfind("-n=", 0) == 0) name = a.substr(3);
+        else if (a.rfind("-e=", 0) == 0) { entropy = a.substr(3); has_entropy = true; }
+        else pos.push_back(a);
+    }
+    auto hex = [](const uint8_t* h) {
+        std::string s;
+        char b[3];
+        for (int i = 0; i < 64; i++) { std::snprintf(b, sizeof b, "%02x", h[i]); s += b; if (i % 4 == 3 && i != 63) s += i % 16 == 15 ? "\n\t\t" : " "; }
+        return s;
+    };
+    uint8_t h[64];
+    int rc;
+    if (cmd == "--zkey-contribute" && pos.size() == 2) {
+        rc = g16_zkey_contribute(pos[0].c_str(), pos[1].c_str(), name.c_str(), has_entropy ? (const uint8_t*)entropy.data() : nullptr,
+                                 entropy.size(), nullptr, h);
+        if (rc == G16_OK) std::printf("Contribution Hash: \n\t\t%s\n", hex(h).c_str());
+    } else if (cmd == "--zkey-beacon" && pos.size() == 4) {
+        std::vector<uint8_t> b;
+        for (size_t i = 0; i + 1 < pos[2].size(); i += 2) b.push_back((uint8_t)std::strtoul(pos[2].substr(i, 2).c_str(), nullptr, 16));
+        rc = g16_zkey_beacon(pos[0].c_str(), pos[1].c_str(), name.c_str(), b.data(), b.size(), (uint32_t)std::atoi(pos[3].c_str()), nullptr, h);
+        if (rc == G16_OK) std::printf("Contribution Hash: \n\t\t%s\n", hex(h).c_str());
+    } else if (cmd == "--zkey-export-vkey" && pos.size() == 2) {
+        std::vector<char> buf(1 << 16);
+        size_t n = buf.size();
+        rc = g16_zkey_export_vkey(pos[0].c_str(), buf.data(), &n);
+        if (rc == G16_ERR_SHORT_BUFFER) {
+            buf.resize(n + 1);
+            n = buf.size();
+            rc = g16_zkey_export_vkey(pos[0].c_str(), buf.data(), &n);
+        }
+        if (rc == G16_OK) {
+            FILE* f = std::fopen(pos[1].c_str(), "wb");
+            if (!f || std::fwrite(buf.data(), 1, n, f) != n || std::fclose(f) != 0) {
+                std::fprintf(stderr, "cannot write %s\n", pos[1].c_str());
+                return 1;
+            }
+        }
+    } else {
+        std::fprintf(stderr, "Usage: prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]\n"
+                             "       prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]\n"
+                             "       prover --zkey-export-vkey <zkey> <verification_key.json>\n");
+        return 2;
+    }
+    if (rc != G16_OK) {
+        std::fprintf(stderr, "%s\n", g16_last_error());
+        return 1;
+    }
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc >= 2 && !std::strcmp(argv[1], "--merkle-tree")) return merkle_cli(argc, argv);
+    if (argc >= 2 && !std::strncmp(argv[1], "--zkey-", 7)) return setup_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--verify") || !std::strcmp(argv[1], "--sanitize"))) return verify_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--serve") || !std::strcmp(argv[1], "--ping") ||
                       !std::strcmp(argv[1], "--stats") || !std::strcmp(argv[1], "--shutdown")))
