@@ -32,6 +32,8 @@ def parse_sections(data):
     """{section type: payload bytes} of a zkey image"""
     _, secs = read_binfile(data, b"zkey")
     return {t: bytes(data[v[0][0]:v[0][0] + v[0][1]]) for t, v in secs.items()}
+
+
 G2_COFACTOR = 2 * Q - R
 
 
@@ -99,7 +101,9 @@ def hash_to_g2(transcript):
             continue
         if f2_is_negative(y):
             y = ((Q - y[0]) % Q, (Q - y[1]) % Q)
-        p = bn.G2.mul((x, y), G2_COFACTOR)
+        # cofactor clearing: the point is NOT in the order-r subgroup yet, so the scalar must not be reduced mod r
+        # (Curve.mul does that): use the Jacobian ladder directly
+        p = bn.G2.to_affine(bn.G2.jmul(bn.G2.to_jac((x, y)), G2_COFACTOR))
         if p is not None:
             return p
 

@@ -49,3 +49,12 @@ def test_native_vkey_export_matches_oracle(pkg, tmp_path, n_public):
     (tmp_path / "bad.zkey").write_bytes(bytes(zk)[:1000])
     with pytest.raises(pkg.G16Error):
         pkg.zkey_export_vkey(str(tmp_path / "bad.zkey"))
+
+
+def test_hash_to_g2_matches_oracle_and_lands_in_the_subgroup(pkg):
+    for tr in (bytes(range(64)), bytes(64), b"\xff" * 64):
+        p = S.hash_to_g2(tr)
+        assert pkg.test_hash(2, tr) == S._g2_lem(p)
+        assert bn.G2.to_affine(bn.G2.jmul(bn.G2.to_jac(p), bn.R)) is None     # order r
+        x, y = p
+        assert bn.f2_mul(y, y) == bn.f2_add(bn.f2_mul(bn.f2_mul(x, x), x), bn.B2)   # on the twist

@@ -603,7 +603,7 @@ def zkey_export_vkey(zkey_path):
 
 
 def test_hash(which, data):
-    out = ctypes.create_string_buffer(64 if which == 0 else 32)
+    out = ctypes.create_string_buffer({0: 64, 1: 32}.get(which, 128))
     _check(lib().g16_test_hash(which, bytes(data), len(data), out))
     return out.raw
 

@@ -1002,17 +1002,18 @@ void Msm<C>::enqueue(const aff* bases_, const uint32_t* scalars, const uint32_t*
         }
     }
     if constexpr (sizeof(pt) <= 128) {
-        if (acc_minb() == 4) {
-            msm_accumulate_kernel<C, 4><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
-                                                              t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
+        // G16_ACC_MINB=5 / 6: 96 / 80 registers (5 / 6 CTAs per SM, 124 / 232 bytes of spills) for comparison
+        if (acc_minb() == 5 || acc_minb() == 6) {
+            if (acc_minb() == 5)
+                msm_accumulate_kernel<C, 5><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
+                                                                  t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
+            else
+                msm_accumulate_kernel<C, 6><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
+                                                                  t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
             launched = true;
         }
-    }
-    if constexpr (sizeof(pt) > 128) {
-        // G2, one thread per task: G16_G2_MINB=3 caps the kernel at 168 registers (3 CTAs per SM, more spills) instead of 255
-        static const int g2_minb = [] { const char* e = std::getenv("G16_G2_MINB"); return e ? std::atoi(e) : 1; }();
-        if (!launched && g2_minb == 3) {
-            msm_accumulate_kernel<C, 3><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
+        if (!launched && acc_minb() == 4) {
+            msm_accumulate_kernel<C, 4><<<agrid, 128, 0, s>>>(bases, entry_vals, order.as<uint32_t>(), t_begin.as<uint32_t>(),
                                                               t_len.as<uint32_t>(), t_out.as<uint32_t>(), prm, buckets.as<pt>(), parts.as<pt>());
             launched = true;
         }

@@ -980,12 +980,16 @@ int g16_h_transform(g16_zkey* zk, int which) {
         G16_CUDA(cudaSetDevice(zk->device));
         cudaStream_t s = zk->s_main;
         uint32_t n = zk->domain_size;
-        G16_CUDA(cudaEventRecord(zk->ev[0], s));
-        r1cs_eval_kernel<<<(n + 127) / 128, 128, 0, s>>>(zk->row_ptr.as<uint32_t>(), zk->col.as<uint32_t>(),
-                                                         zk->val.as<fe_t>(), zk->w.as<fe_t>(), n, zk->pa.as<fe_t>(),
-                                                         zk->pb.as<fe_t>(), zk->pc.as<fe_t>());
-        G16_CUDA(cudaGetLastError());
-        G16_LAUNCHED(1);
+        if (!zk->witness_enqueued) G16_CUDA(cudaEventRecord(zk->ev[0], s));   // else g16_prove_begin marked the proof's start
+        cudaEvent_t t0 = zk->ev[15];
+        G16_CUDA(cudaEventRecord(t0, s));
+        if (which) {   // a rank that owns no polynomial has nothing to evaluate
+            r1cs_eval_kernel<<<(n + 127) / 128, 128, 0, s>>>(zk->row_ptr.as<uint32_t>(), zk->col.as<uint32_t>(),
+                                                             zk->val.as<fe_t>(), zk->w.as<fe_t>(), n, zk->pa.as<fe_t>(),
+                                                             zk->pb.as<fe_t>(), zk->pc.as<fe_t>());
+            G16_CUDA(cudaGetLastError());
+            G16_LAUNCHED(1);
+        }
         G16_CUDA(cudaEventRecord(zk->ev[1], s));
         if (which & 1) zk->dom.to_odd_coset(zk->pa.as<fe_t>(), s);
         if (which & 2) zk->dom.to_odd_coset(zk->pb.as<fe_t>(), s);
@@ -993,7 +997,7 @@ int g16_h_transform(g16_zkey* zk, int which) {
         G16_CUDA(cudaEventRecord(zk->ev[2], s));
         G16_CUDA(cudaStreamSynchronize(s));
         float ms = 0;
-        cudaEventElapsedTime(&ms, zk->ev[0], zk->ev[1]); zk->t_transform_ms[0] = ms;
+        cudaEventElapsedTime(&ms, t0, zk->ev[1]); zk->t_transform_ms[0] = ms;
         cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_transform_ms[1] = ms;
         return (int)G16_OK;
     });

@@ -480,9 +480,11 @@ int g16_test_hash(int which, const uint8_t* data, size_t n, uint8_t* out) {
         h.update(data, n);
         bytes d = h.digest();
         std::memcpy(out, d.data(), 64);
-    } else {
+    } else if (which == 1) {
         bytes d = sha256(data, n);
         std::memcpy(out, d.data(), 32);
+    } else {   // 2: hashToG2 of a transcript -> the 128-byte point record
+        put_g2(out, hash_to_g2(bytes(data, data + n)));
     }
     return G16_OK;
 }
