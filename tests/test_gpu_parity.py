@@ -41,6 +41,7 @@ def test_field_ops(pkg, field, p):
     assert ints(pkg.field_op(field, 2, A, B)) == [(x - y) % p for x, y in zip(a, b)]
     assert ints(pkg.field_op(field, 3, A)) == [(x << 256) % p for x in a]
     assert ints(pkg.field_op(field, 4, A)) == [x * rinv % p for x in a]
+    assert ints(pkg.field_op(field, 6, A)) == [x * x * rinv % p for x in a]      # the dedicated squaring (kept as an option: field.cuh)
     sub = a[:200]
     got = ints(pkg.field_op(field, 5, b"".join(map(le, sub))))
     # Montgomery inverse: inv(aR) = a^-1 R, i.e. got * x == R^2

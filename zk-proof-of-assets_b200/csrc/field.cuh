@@ -125,6 +125,62 @@ __device__ __forceinline__ void mad_row_shift(uint32_t (&out)[8], uint32_t& lo0,
           "r"(x2), "r"(x3), "r"(y));
 }
 
+
+// ---- building blocks of the dedicated squaring ------------------------------------------------------------------
+// acc pairs += {x...} * y on aligned register pairs, carry out returned; 1, 2 and 3 products (4 = mad_row_c)
+__device__ __forceinline__ uint32_t mad_pairs1_c(uint32_t& a0, uint32_t& a1, uint32_t x0, uint32_t y) {
+    uint32_t c;
+    asm("mad.lo.cc.u32 %0, %3, %4, %0;\n\t"
+        "madc.hi.cc.u32 %1, %3, %4, %1;\n\t"
+        "addc.u32 %2, 0, 0;"
+        : "+r"(a0), "+r"(a1), "=r"(c)
+        : "r"(x0), "r"(y));
+    return c;
+}
+__device__ __forceinline__ uint32_t mad_pairs2_c(uint32_t& a0, uint32_t& a1, uint32_t& a2, uint32_t& a3, uint32_t x0, uint32_t x1,
+                                                 uint32_t y) {
+    uint32_t c;
+    asm("mad.lo.cc.u32 %0, %5, %7, %0;\n\t"
+        "madc.hi.cc.u32 %1, %5, %7, %1;\n\t"
+        "madc.lo.cc.u32 %2, %6, %7, %2;\n\t"
+        "madc.hi.cc.u32 %3, %6, %7, %3;\n\t"
+        "addc.u32 %4, 0, 0;"
+        : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3), "=r"(c)
+        : "r"(x0), "r"(x1), "r"(y));
+    return c;
+}
+__device__ __forceinline__ uint32_t mad_pairs3_c(uint32_t& a0, uint32_t& a1, uint32_t& a2, uint32_t& a3, uint32_t& a4, uint32_t& a5,
+                                                 uint32_t x0, uint32_t x1, uint32_t x2, uint32_t y) {
+    uint32_t c;
+    asm("mad.lo.cc.u32 %0, %7, %10, %0;\n\t"
+        "madc.hi.cc.u32 %1, %7, %10, %1;\n\t"
+        "madc.lo.cc.u32 %2, %8, %10, %2;\n\t"
+        "madc.hi.cc.u32 %3, %8, %10, %3;\n\t"
+        "madc.lo.cc.u32 %4, %9, %10, %4;\n\t"
+        "madc.hi.cc.u32 %5, %9, %10, %5;\n\t"
+        "addc.u32 %6, 0, 0;"
+        : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3), "+r"(a4), "+r"(a5), "=r"(c)
+        : "r"(x0), "r"(x1), "r"(x2), "r"(y));
+    return c;
+}
+__device__ __forceinline__ uint32_t mad_pairs4_c(uint32_t& a0, uint32_t& a1, uint32_t& a2, uint32_t& a3, uint32_t& a4, uint32_t& a5,
+                                                 uint32_t& a6, uint32_t& a7, uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3,
+                                                 uint32_t y) {
+    uint32_t c;
+    asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\t"
+        "madc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %2;\n\t"
+        "madc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %4;\n\t"
+        "madc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, %6;\n\t"
+        "madc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+        "addc.u32 %8, 0, 0;"
+        : "+r"(a0), "+r"(a1), "+r"(a2), "+r"(a3), "+r"(a4), "+r"(a5), "+r"(a6), "+r"(a7), "=r"(c)
+        : "r"(x0), "r"(x1), "r"(x2), "r"(x3), "r"(y));
+    return c;
+}
+
 template <class P>
 struct Field {
     typedef fe_t el;
@@ -287,7 +343,125 @@ struct Field {
         return o;
     }
 
+    // The squaring every kernel uses is the general product: the dedicated form below has 28 fewer wide multiply-adds
+    // but was measured SLOWER inside the kernels that matter (H accumulation 4.61 -> 4.75 ms at 2^21, 33.7 -> 34.7 ms at
+    // 2^24; Poseidon tree unchanged): its separated reduction and the doubling add ~130 carry-chain ALU instructions of
+    // dependent latency and 40 more bytes of spills at 128 registers, and those kernels are limited by dependency
+    // stalls as much as by the pipe (ncu: stalled_wait above math_pipe_throttle).
     static __device__ __forceinline__ el sqr(const el& a) { return mul(a, a); }
+
+    // Dedicated Montgomery squaring (kept, tested through g16_test_field_op op 6): the 28 cross products a_i a_j (i < j)
+    // once, doubled, plus the 8 squares = 36 wide multiply-adds instead of 64, then a separated reduction (8 rows of
+    // m * MOD): 108 of the integer pipe's slots against 136 for mul(a, a).  Cross products of odd / even limb distance go
+    // to two accumulators one limb apart (O holds limb k+1 at index k), so that every product lands on an aligned
+    // register pair like in mul(); rows are ordered so that a chain's carry always lands at or above everything written
+    // so far.  Limb-level model: tools/sqrsim.py.
+    static __device__ __forceinline__ el sqr_dedicated(const el& a) {
+        const uint32_t a0 = a.v[0], a1 = a.v[1], a2 = a.v[2], a3 = a.v[3], a4 = a.v[4], a5 = a.v[5], a6 = a.v[6], a7 = a.v[7];
+        uint32_t E[16], O[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) E[k] = O[k] = 0;
+        // row 0: a0 * {a1,a3,a5,a7} -> O[0..7], a0 * {a2,a4,a6} -> E[2..7]
+        O[8] += mad_pairs4_c(O[0], O[1], O[2], O[3], O[4], O[5], O[6], O[7], a1, a3, a5, a7, a0);
+        E[8] += mad_pairs3_c(E[2], E[3], E[4], E[5], E[6], E[7], a2, a4, a6, a0);
+        // row 1: a1 * {a2,a4,a6} -> O[2..7], a1 * {a3,a5,a7} -> E[4..9]
+        O[8] += mad_pairs3_c(O[2], O[3], O[4], O[5], O[6], O[7], a2, a4, a6, a1);
+        E[10] += mad_pairs3_c(E[4], E[5], E[6], E[7], E[8], E[9], a3, a5, a7, a1);
+        // row 2: a2 * {a3,a5,a7} -> O[4..9], a2 * {a4,a6} -> E[6..9]
+        O[10] += mad_pairs3_c(O[4], O[5], O[6], O[7], O[8], O[9], a3, a5, a7, a2);
+        E[10] += mad_pairs2_c(E[6], E[7], E[8], E[9], a4, a6, a2);
+        // row 3: a3 * {a4,a6} -> O[6..9], a3 * {a5,a7} -> E[8..11]
+        O[10] += mad_pairs2_c(O[6], O[7], O[8], O[9], a4, a6, a3);
+        E[12] += mad_pairs2_c(E[8], E[9], E[10], E[11], a5, a7, a3);
+        // row 4: a4 * {a5,a7} -> O[8..11], a4 * a6 -> E[10..11]
+        O[12] += mad_pairs2_c(O[8], O[9], O[10], O[11], a5, a7, a4);
+        E[12] += mad_pairs1_c(E[10], E[11], a6, a4);
+        // row 5: a5 * a6 -> O[10..11], a5 * a7 -> E[12..13]
+        O[12] += mad_pairs1_c(O[10], O[11], a6, a5);
+        E[14] += mad_pairs1_c(E[12], E[13], a7, a5);
+        // row 6: a6 * a7 -> O[12..13]
+        O[14] += mad_pairs1_c(O[12], O[13], a7, a6);
+        // C = E + (O << 32): 15 limbs of carry chain (E[0] = E[1] = 0: no cross product sits at positions 0, 1 of E)
+        uint32_t T[16];
+        T[0] = 0;
+        asm("add.cc.u32 %0, %15, %30;\n\t"     // T1 = E1 + O0
+            "addc.cc.u32 %1, %16, %31;\n\t"
+            "addc.cc.u32 %2, %17, %32;\n\t"
+            "addc.cc.u32 %3, %18, %33;\n\t"
+            "addc.cc.u32 %4, %19, %34;\n\t"
+            "addc.cc.u32 %5, %20, %35;\n\t"
+            "addc.cc.u32 %6, %21, %36;\n\t"
+            "addc.cc.u32 %7, %22, %37;\n\t"
+            "addc.cc.u32 %8, %23, %38;\n\t"
+            "addc.cc.u32 %9, %24, %39;\n\t"
+            "addc.cc.u32 %10, %25, %40;\n\t"
+            "addc.cc.u32 %11, %26, %41;\n\t"
+            "addc.cc.u32 %12, %27, %42;\n\t"
+            "addc.cc.u32 %13, %28, %43;\n\t"
+            "addc.u32 %14, %29, %44;"
+            : "=r"(T[1]), "=r"(T[2]), "=r"(T[3]), "=r"(T[4]), "=r"(T[5]), "=r"(T[6]), "=r"(T[7]), "=r"(T[8]), "=r"(T[9]),
+              "=r"(T[10]), "=r"(T[11]), "=r"(T[12]), "=r"(T[13]), "=r"(T[14]), "=r"(T[15])
+            : "r"(E[1]), "r"(E[2]), "r"(E[3]), "r"(E[4]), "r"(E[5]), "r"(E[6]), "r"(E[7]), "r"(E[8]), "r"(E[9]), "r"(E[10]),
+              "r"(E[11]), "r"(E[12]), "r"(E[13]), "r"(E[14]), "r"(E[15]), "r"(O[0]), "r"(O[1]), "r"(O[2]), "r"(O[3]), "r"(O[4]),
+              "r"(O[5]), "r"(O[6]), "r"(O[7]), "r"(O[8]), "r"(O[9]), "r"(O[10]), "r"(O[11]), "r"(O[12]), "r"(O[13]), "r"(O[14]));
+        // double (the cross sum is below 2^511: no bit falls off the top)
+#pragma unroll
+        for (int k = 15; k > 0; k--) T[k] = __funnelshift_l(T[k - 1], T[k], 1);
+        // + a_i^2 at limbs (2i, 2i+1): one carry chain through all sixteen limbs
+        asm("mad.lo.cc.u32 %0, %16, %16, %0;\n\t"
+            "madc.hi.cc.u32 %1, %16, %16, %1;\n\t"
+            "madc.lo.cc.u32 %2, %17, %17, %2;\n\t"
+            "madc.hi.cc.u32 %3, %17, %17, %3;\n\t"
+            "madc.lo.cc.u32 %4, %18, %18, %4;\n\t"
+            "madc.hi.cc.u32 %5, %18, %18, %5;\n\t"
+            "madc.lo.cc.u32 %6, %19, %19, %6;\n\t"
+            "madc.hi.cc.u32 %7, %19, %19, %7;\n\t"
+            "madc.lo.cc.u32 %8, %20, %20, %8;\n\t"
+            "madc.hi.cc.u32 %9, %20, %20, %9;\n\t"
+            "madc.lo.cc.u32 %10, %21, %21, %10;\n\t"
+            "madc.hi.cc.u32 %11, %21, %21, %11;\n\t"
+            "madc.lo.cc.u32 %12, %22, %22, %12;\n\t"
+            "madc.hi.cc.u32 %13, %22, %22, %13;\n\t"
+            "madc.lo.cc.u32 %14, %23, %23, %14;\n\t"
+            "madc.hi.u32 %15, %23, %23, %15;"
+            : "+r"(T[0]), "+r"(T[1]), "+r"(T[2]), "+r"(T[3]), "+r"(T[4]), "+r"(T[5]), "+r"(T[6]), "+r"(T[7]), "+r"(T[8]),
+              "+r"(T[9]), "+r"(T[10]), "+r"(T[11]), "+r"(T[12]), "+r"(T[13]), "+r"(T[14]), "+r"(T[15])
+            : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(a4), "r"(a5), "r"(a6), "r"(a7));
+        // separated Montgomery reduction in the shifting even/odd frame: F = limbs f..f+7 of the running value
+        uint32_t F[8], G[8], hi = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) F[k] = T[k];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            uint32_t m = F[0] * P::INV;
+            mul_row(G, P::mod(1), P::mod(3), P::mod(5), P::mod(7), m);                    // limbs f+1 .. f+8
+            uint32_t c = mad_row_c(F, P::mod(0), P::mod(2), P::mod(4), P::mod(6), m);     // F[0] becomes 0, carry at limb f+8
+            uint32_t t, h1, N[8];
+            asm("add.cc.u32 %0, %2, %3;\n\t"
+                "addc.u32 %1, 0, 0;"
+                : "=r"(t), "=r"(h1)
+                : "r"(T[8 + i]), "r"(c + hi));
+            asm("add.cc.u32 %0, %9, %16;\n\t"
+                "addc.cc.u32 %1, %10, %17;\n\t"
+                "addc.cc.u32 %2, %11, %18;\n\t"
+                "addc.cc.u32 %3, %12, %19;\n\t"
+                "addc.cc.u32 %4, %13, %20;\n\t"
+                "addc.cc.u32 %5, %14, %21;\n\t"
+                "addc.cc.u32 %6, %15, %22;\n\t"
+                "addc.cc.u32 %7, %24, %23;\n\t"
+                "addc.u32 %8, %25, 0;"
+                : "=r"(N[0]), "=r"(N[1]), "=r"(N[2]), "=r"(N[3]), "=r"(N[4]), "=r"(N[5]), "=r"(N[6]), "=r"(N[7]), "=r"(hi)
+                : "r"(F[1]), "r"(F[2]), "r"(F[3]), "r"(F[4]), "r"(F[5]), "r"(F[6]), "r"(F[7]), "r"(G[0]), "r"(G[1]), "r"(G[2]),
+                  "r"(G[3]), "r"(G[4]), "r"(G[5]), "r"(G[6]), "r"(G[7]), "r"(t), "r"(h1));
+#pragma unroll
+            for (int k = 0; k < 8; k++) F[k] = N[k];
+        }
+        final_sub(F);   // a < MOD: the reduced value is below 2 MOD < 2^255, so hi is 0 here
+        el o;
+#pragma unroll
+        for (int k = 0; k < 8; k++) o.v[k] = F[k];
+        return o;
+    }
 
     static __device__ __forceinline__ el to_mont(const el& a) { return mul(r2(), a); }
     static __device__ __forceinline__ el from_mont(const el& a) {

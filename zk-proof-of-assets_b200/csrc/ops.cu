@@ -85,6 +85,7 @@ __global__ void field_op_kernel(int op, const fe_t* a, const fe_t* b, fe_t* o, s
         case 2: r = F::sub(x, y); break;
         case 3: r = F::to_mont(x); break;
         case 4: r = F::from_mont(x); break;
+        case 6: r = F::sqr_dedicated(x); break;
         default: r = F::inv(x); break;
     }
     st_fe(o + i, r);

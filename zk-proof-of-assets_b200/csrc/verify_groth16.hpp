@@ -198,10 +198,14 @@ inline bool verify_groth16(const char* vkey, size_t vkey_len, const char* pub, s
     vkx.inf = vkx.p.inf;
     G1J nA = A;
     nA.p.y = HFq::neg(A.p.y);
-    f12 f = miller_loop(B.p, B.inf, nA.p, nA.inf);
-    f = f12_mul(f, miller_loop(beta.p, beta.inf, alpha.p, alpha.inf));
-    f = f12_mul(f, miller_loop(gamma.p, gamma.inf, vkx.p, vkx.inf));
-    f = f12_mul(f, miller_loop(delta.p, delta.inf, C.p, C.inf));
+    // e(-A, B) e(alpha, beta) e(vk_x, gamma) e(C, delta) == 1: one Miller loop over the four pairs, one final exponentiation
+    auto pair = [](const G2J& q, const G1J& p) {
+        PairingInput x{q.p, p.p};
+        x.q.inf = q.inf;
+        x.p.inf = p.inf;
+        return x;
+    };
+    f12 f = miller_loop_multi({pair(B, nA), pair(beta, alpha), pair(gamma, vkx), pair(delta, C)});
     return f12_eq(final_exponentiate(f), f12_one());
 }
 
