@@ -209,6 +209,19 @@ int g16_merkle_find(const g16_merkle* t, const uint8_t hash[32], uint64_t from, 
  * <dir>/merkle_root.json and <dir>/merkle_proofs.json in the reference's byte layout (scripts/README.md:633-673).
  * poa_input_json may be NULL (root only, empty proofs file). */
 int g16_merkle_files(const char* anon_set_csv, const char* poa_input_json, const char* output_dir, const g16_opts* opts);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The root of the same tree as
+ * g16_merkle_build + g16_merkle_root, with every buffer supplied: d_rows = n_rows x (address[32] | balance[32]) in DEVICE
+ * memory (standard form, below r: NOT checked here, the rows never visit the host), d_root = 32 bytes of DEVICE memory,
+ * stream = a cudaStream_t (NULL = the default stream) of the CURRENT device.  The node levels live in a file-scope
+ * `static __device__` array of 2 * G16_MERKLE_STATIC_MAX_ROWS * 32 bytes = 4 MiB (csrc/poseidon.cu), which every GPU
+ * that loads the library holds until exit.  n_rows > G16_MERKLE_STATIC_MAX_ROWS is rejected (G16_ERR_GENERIC, message
+ * in g16_last_error).  Calls no cudaMalloc/cudaFree or allocating library routine and does not synchronise: the result
+ * is in d_root once `stream` reaches this point.  Every call on a GPU shares the array: calls that overlap on the GPU
+ * (different streams, threads or processes sharing a context) RACE -- order them on one stream or with events.  A
+ * device's first call uploads the Poseidon constants (cudaMemcpyToSymbol): make it outside graph capture. */
+#define G16_MERKLE_STATIC_MAX_ROWS 65536
+int g16_merkle_root_static(const void* d_rows, size_t n_rows, void* d_root, void* stream);
 
 
 /* ---- phase-2 ceremony steps and verification-key export (file level) ----------------------

@@ -43,7 +43,7 @@ ABI_SYMBOLS = [
     "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace", "g16_h_transform", "g16_h_buffer",
     "g16_prove_partial_joined", "g16_prove_begin", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
-    "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files",
+    "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files", "g16_merkle_root_static",
     "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash",
 ]
 SYNTH_SYMBOLS = [
@@ -137,6 +137,7 @@ def lib():
         L.g16_merkle_proof.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_merkle_find.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p]
         L.g16_merkle_files.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
+        L.g16_merkle_root_static.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_zkey_contribute.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
                                           ctypes.c_void_p, ctypes.c_void_p]
         L.g16_zkey_beacon.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
@@ -566,6 +567,17 @@ def merkle_files(anon_set_csv, poa_input_json, output_dir, device=-1):
     o = make_opts(device=device)
     _check(lib().g16_merkle_files(os.fsencode(anon_set_csv), os.fsencode(poa_input_json) if poa_input_json else None,
                                   os.fsencode(output_dir), ctypes.byref(o)))
+
+
+MERKLE_STATIC_MAX_ROWS = 65536
+
+
+def merkle_root_static(d_rows, n_rows, d_root, stream=None):
+    """g16_merkle_root_static: the tree's root with every buffer supplied -- d_rows / d_root are DEVICE addresses (ints) on
+    the current device, stream a cudaStream_t handle (int) or None.  Allocates nothing, does not synchronise; all calls
+    on a GPU share one fixed 4 MiB device array, so overlapping calls race.  At most MERKLE_STATIC_MAX_ROWS rows."""
+    _check(lib().g16_merkle_root_static(ctypes.c_void_p(d_rows), n_rows, ctypes.c_void_p(d_root),
+                                        ctypes.c_void_p(stream) if stream else None))
 
 
 # ---- phase-2 ceremony steps + vkey export (scripts/g16_setup.sh:254-295) ------------------------------------------

@@ -20,6 +20,12 @@
 using namespace g16;
 using namespace g16h;
 
+// ---- g16_merkle_root_static: the tree's node levels in a fixed device array, for callers that cannot allocate ----
+// Every level of a tree of up to G16_MERKLE_STATIC_MAX_ROWS leaves (2 * max * 32 bytes = 4 MiB).  Held by every GPU that
+// loads the library until exit.  In host code the name below is a host-side stand-in, not a device address: the kernels
+// are given the pointer cudaGetSymbolAddress returns, looked up once per device with that device current.
+static __device__ __align__(256) unsigned char g_merkle_static_nodes[2 * size_t(G16_MERKLE_STATIC_MAX_ROWS) * 32];
+
 namespace {
 
 constexpr int POS_T = 3, POS_RF = 8, POS_RP = 57;
@@ -196,6 +202,24 @@ void hash_level(const fe_t* in, fe_t* out, size_t n, size_t n_out, cudaStream_t 
     G16_LAUNCHED(1);
 }
 
+// ---- g16_merkle_root_static: set-up of the fixed device array declared at the top of this file ----
+fe_t* static_nodes() {   // once per device; no allocation
+    static std::mutex mu;
+    static fe_t* addr[64] = {nullptr};
+    int dev = 0;
+    G16_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw std::runtime_error("CUDA error: device ordinal beyond the 64 this entry point tracks");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_merkle_static_nodes);
+        if (e != cudaSuccess || !p)
+            throw std::runtime_error(std::string("CUDA error: cudaGetSymbolAddress(g_merkle_static_nodes): ") + cudaGetErrorString(e));
+        addr[dev] = static_cast<fe_t*>(p);
+    }
+    return addr[dev];
+}
+
 }  // namespace
 
 struct g16_merkle {
@@ -339,6 +363,38 @@ int g16_merkle_find(const g16_merkle* t, const uint8_t hash[32], uint64_t from, 
         unsigned long long h = 0;
         G16_CUDA(cudaMemcpy(&h, found.p, 8, cudaMemcpyDeviceToHost));
         *index = h;
+        return (int)G16_OK;
+    });
+}
+
+// The root of the anonymity-set tree with every buffer supplied: rows and root by the caller (device memory), the node
+// levels in g_merkle_static_nodes.  Same kernels and level order as g16_merkle_build; calls no cudaMalloc / cudaFree,
+// creates no stream or event, does not synchronise.  All calls on one GPU share the array: calls that overlap on the
+// GPU race.  Nothing needs clearing between calls: the leaf launch writes all `size` leaves (hashes, then zero leaves),
+// and each level above is written in full before it is read.
+int g16_merkle_root_static(const void* d_rows, size_t n_rows, void* d_root, void* stream) {
+    return guarded([&]() {
+        if (!d_rows || !d_root) return fail(G16_ERR_GENERIC, "null argument");
+        if (!n_rows) return fail(G16_ERR_GENERIC, "merkle: empty anonymity set");
+        if (n_rows > size_t(G16_MERKLE_STATIC_MAX_ROWS))
+            return fail(G16_ERR_GENERIC, "merkle: " + std::to_string(n_rows) + " rows exceed the " +
+                                             std::to_string(G16_MERKLE_STATIC_MAX_ROWS) +
+                                             " that g16_merkle_root_static's fixed device array holds; use g16_merkle_build");
+        use_device(nullptr);   // the current device; fails loudly without one
+        upload_params();       // cudaMemcpyToSymbol on a device's first call only
+        fe_t* nodes = static_nodes();
+        cudaStream_t s = static_cast<cudaStream_t>(stream);
+        size_t size = 1;
+        while (size < n_rows) size *= 2;
+        fe_t* root = static_cast<fe_t*>(d_root);
+        // leaves: hashes of the rows, zero leaves up to `size` (written by the same launch, so stale contents never show)
+        fe_t* level = size == 1 ? root : nodes;
+        hash_level(static_cast<const fe_t*>(d_rows), level, n_rows, size, s);
+        for (size_t w = size / 2; w >= 1; w /= 2) {
+            fe_t* up = w == 1 ? root : level + 2 * w;
+            hash_level(level, up, w, w, s);
+            level = up;
+        }
         return (int)G16_OK;
     });
 }
