@@ -105,6 +105,15 @@ int g16_prove_begin(g16_zkey* zk);
 int g16_h_transform(g16_zkey* zk, int which);
 int g16_h_buffer(g16_zkey* zk, int poly /*0 A, 1 B, 2 C*/, void** d_ptr, uint64_t* h_lo, uint64_t* h_n);
 int g16_prove_partial_joined(g16_zkey* zk, const void* d_a, const void* d_b, const void* d_c, uint8_t* partial_out);
+/* With G >= 6 ranks each transform is split over TWO ranks (one polynomial's transform on one rank bounds a sharded
+ * proof otherwise): X[k] = Y0[k mod n/2] + inc w^k Y1[k mod n/2], where Yt is the odd-coset transform, on the domain of
+ * half the size, of the polynomial's coefficients of parity t (ffjavascript's engine_fft.js does the same radix-2 split
+ * across its worker threads).  g16_h_transform_half(zk, poly, parity) leaves Yt (inc folded in for t = 1) TWICE in
+ * polynomial `poly`'s buffer, so that slices [h_lo, h_lo + h_n) cut exactly as from a whole transform;
+ * g16_prove_partial_joined_halves takes this rank's six slices, in the order A even, A odd, B even, B odd, C even,
+ * C odd, and recombines the halves inside the join. */
+int g16_h_transform_half(g16_zkey* zk, int poly /*0 A, 1 B, 2 C*/, int parity);
+int g16_prove_partial_joined_halves(g16_zkey* zk, const void* const d_halves[6], uint8_t* partial_out);
 
 /* ---- verification: replaces `snarkjs groth16 verify <vkey.json> <public.json> <proof.json>`
  * (scripts/g16_verify.sh:212-216), the consumer of the prover's output.  Host code only -- works without a GPU.

@@ -557,6 +557,41 @@ def test_batch_apply_key_is_the_contribute_update_of_sections_8_and_9(pkg, small
     assert not V.verify(f["vkey"], json.loads(public), json.loads(proof))     # the old delta no longer fits
 
 
+@pytest.mark.parametrize("n_vars,n_public,n_cons,shards", [(85, 2, 100, 1), (85, 2, 100, 3), (30000, 1, 32000, 1), (200000, 13, 262130, 5)])
+def test_split_transform_halves_recombine_bit_exact(pkg, n_vars, n_public, n_cons, shards):
+    """g16_h_transform_half + g16_prove_partial_joined_halves: the six half transforms (coefficients split by parity, half
+    domain, recombined inside the join) give the same proof as the whole transforms, for every shard's H range --
+    including ranges that straddle the middle of the domain.  2^15 and 2^18 points: one- and two-pass half transforms."""
+    import torch
+    sy = pkg.Synth(n_vars, n_public, n_cons, 11, 12)
+    zkey, wtns = sy.write()
+    r, s = 0xABCDEF0123456789 << 64, 0x1F2E3D4C5B6A7988 << 128
+    handles = [pkg.ZKey(zkey, shard_rank=k, shard_count=shards) for k in range(shards)]
+    n = handles[0].domain_size
+    halves = []
+    for poly in range(3):                     # any handle can transform: the polynomial buffers are whole on every rank
+        for parity in range(2):
+            h = handles[(2 * poly + parity) % shards]
+            h.load_witness(wtns)
+            h.h_transform_half(poly, parity)
+            ptr, _, _ = h.h_buffer(poly)
+            buf = torch.as_tensor(pkg._DevMem(ptr, n * 32), device="cuda").clone()
+            assert torch.equal(buf[:n * 16], buf[n * 16:])      # the half, twice
+            halves.append(buf)
+    want, got = b"", b""
+    for h in handles:
+        h.load_witness(wtns)
+        want += h.prove_partial()
+        _, lo, cnt = h.h_buffer(0)
+        got += h.prove_partial_joined_halves([b.data_ptr() + lo * 32 for b in halves])
+    # partial sums are projective (their representation depends on the order of additions): compare the proofs
+    assert handles[0].combine(got, r=r, s=s) == handles[0].combine(want, r=r, s=s)
+    proof, _ = handles[0].combine(got, r=r, s=s)
+    assert json.loads(proof) == g16.proof_object(*sy.expected(r, s))
+    for h in handles:
+        h.close()
+
+
 SHARD_WORKER = r'''
 import os, sys, json
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
@@ -577,10 +612,11 @@ dist.barrier(); dist.destroy_process_group()
 '''
 
 
-@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("world", [2, 3, 6, 7])
 def test_prove_sharded_ranks(pkg, small_fixture, tmp_path, world):
     """One proof over several ranks (base-range shards, 768-byte partial gather; then also with the transforms
-    spread over the ranks and an all-to-all of their slices) == the whole-key proof, on every rank."""
+    spread over the ranks and an all-to-all of their slices) == the whole-key proof, on every rank.  From six ranks on
+    each transform is split in halves over two ranks (7: an H range that straddles the middle of the domain)."""
     import socket
     import sys
     f = small_fixture

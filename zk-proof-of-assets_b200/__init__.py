@@ -41,7 +41,7 @@ ABI_SYMBOLS = [
     "g16_msm_stats", "g16_h_scalars", "g16_coset_ntt_dev", "g16_coset_ntt_host", "g16_test_field_op",
     "g16_test_curve_op", "g16_last_timings", "g16_last_msm_stats", "g16_bench_int_pipe", "g16_h_pipeline_dev",
     "g16_last_accumulate_ms", "g16_launch_count", "g16_last_trace", "g16_h_transform", "g16_h_buffer",
-    "g16_prove_partial_joined", "g16_prove_begin", "g16_verify", "g16_sanitize",
+    "g16_prove_partial_joined", "g16_prove_begin", "g16_h_transform_half", "g16_prove_partial_joined_halves", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
     "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files", "g16_merkle_root_static",
     "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash",
@@ -123,6 +123,8 @@ def lib():
         L.g16_h_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_prove_partial_joined.argtypes = [ctypes.c_void_p] * 5
         L.g16_prove_begin.argtypes = [ctypes.c_void_p]
+        L.g16_h_transform_half.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
+        L.g16_prove_partial_joined_halves.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_sanitize.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
                                    ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_verify.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
@@ -308,6 +310,17 @@ class ZKey:
     def prove_partial_joined(self, d_a, d_b, d_c):
         out = ctypes.create_string_buffer(PARTIAL_BYTES)
         _check(lib().g16_prove_partial_joined(self._h, d_a, d_b, d_c, out))
+        return out.raw
+
+    def h_transform_half(self, poly, parity):
+        """half of polynomial `poly`'s coset transform (the coefficients of one parity), left twice in that polynomial's buffer"""
+        _check(lib().g16_h_transform_half(self._h, poly, parity))
+
+    def prove_partial_joined_halves(self, ptrs):
+        """ptrs: six device addresses -- this rank's slices of A even, A odd, B even, B odd, C even, C odd"""
+        arr = (ctypes.c_void_p * 6)(*ptrs)
+        out = ctypes.create_string_buffer(PARTIAL_BYTES)
+        _check(lib().g16_prove_partial_joined_halves(self._h, arr, out))
         return out.raw
 
     def combine(self, partials, r=None, s=None, style=STYLE_RAPIDSNARK):
@@ -724,6 +737,11 @@ def transform_owner(poly, world):
     return poly % min(world, 3)
 
 
+def split_transforms(world):
+    """from six ranks on, each polynomial's transform is split in halves over two ranks: rank 2 * poly + parity"""
+    return world >= 6 and os.environ.get("G16_SPLIT_TRANSFORMS", "1") != "0"
+
+
 class _DevMem:
     """a device allocation owned by libg16b200, exposed to torch through __cuda_array_interface__ (no copy)"""
 
@@ -760,19 +778,49 @@ def exchange_h_slices(zk, group=None):
     return out
 
 
+def exchange_h_halves(zk, group=None):
+    """exchange_h_slices for transforms split in halves: ranks 0..5 own (polynomial, parity) = (rank // 2, rank % 2); ONE
+    all-to-all moves every owner's buffer, cut by the ranks' H ranges, to everyone.  -> a uint8 device tensor of six
+    slices in the order A even, A odd, B even, B odd, C even, C odd."""
+    import torch
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = zk.domain_size
+    sizes = [(shard_range(n, g, world)[1] - shard_range(n, g, world)[0]) * 32 for g in range(world)]
+    xdev = dev if dist.get_backend(group) == "nccl" else torch.device("cpu")
+    recv = torch.empty(6 * sizes[rank], dtype=torch.uint8, device=xdev)
+    out_split = [sizes[rank] if g < 6 else 0 for g in range(world)]
+    if rank < 6:
+        ptr, lo, cnt = zk.h_buffer(rank // 2)
+        assert cnt * 32 == sizes[rank] and lo == shard_range(n, rank, world)[0]
+        dist.all_to_all_single(recv, torch.as_tensor(_DevMem(ptr, n * 32), device=dev).to(xdev), out_split, sizes, group=group)
+    else:
+        dist.all_to_all_single(recv, torch.empty(0, dtype=torch.uint8, device=xdev), out_split, [0] * world, group=group)
+    return recv.to(dev)
+
+
 def prove_sharded_distributed(zk, wtns=None, r=None, s=None, style=STYLE_RAPIDSNARK, group=None):
     """One proof over all ranks with the three coset transforms spread over the ranks as well: transform the
-    polynomials this rank owns, all-to-all the slices, MSMs on this rank's base ranges + join on its H range, all-gather
-    the 768-byte partials, combine.  NCCL only (the slices are device tensors)."""
+    polynomials this rank owns (from six ranks on: one HALF of one polynomial's transform), all-to-all the slices, MSMs on
+    this rank's base ranges + join on its H range, all-gather the 768-byte partials, combine."""
+    import torch
     import torch.distributed as dist
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     if wtns is not None:
         zk.load_witness(wtns)
     zk.prove_begin()      # the witness MSMs depend on neither the transforms nor the exchange: they run underneath both
+    if split_transforms(world):
+        if rank < 6:
+            zk.h_transform_half(rank // 2, rank % 2)
+        got = exchange_h_halves(zk, group)
+        torch.cuda.current_stream().synchronize()
+        step = got.numel() // 6
+        partial = zk.prove_partial_joined_halves([got.data_ptr() + i * step for i in range(6)])
+        return zk.combine(all_gather_partials(partial, group), r=r, s=s, style=style)
     mask = sum(1 << p for p in range(3) if transform_owner(p, world) == rank)
     zk.h_transform(mask)
     a, b, c = exchange_h_slices(zk, group)
-    import torch
     torch.cuda.current_stream().synchronize()
     partials = all_gather_partials(zk.prove_partial_joined(a.data_ptr(), b.data_ptr(), c.data_ptr()), group)
     return zk.combine(partials, r=r, s=s, style=style)

@@ -268,6 +268,43 @@ static __global__ void ntt_join_kernel(const fe_t* __restrict__ A, const fe_t* _
     st_fe(P + i, Fr::from_mont(v));
 }
 
+// ---- a transform split over two devices (sharded proofs on >= 6 GPUs) ------------------------------------------------
+// With the coefficients split by parity, c[2m+t], the coset evaluations are
+//     X[k] = Y0[k mod n/2] + inc w^k Y1[k mod n/2],   Yt = odd-coset transform, on the HALF domain, of the polynomial c[2m+t]
+// and c[2m+t] = 1/2 iNTT_half(b_t)[m] with b_t[i] = (a[i] + (-1)^t a[i + n/2]) w^(-i t): the first decimation-in-frequency
+// level.  The half domain's coset factor is w^m (its `inc` is the full domain's w), so the full domain's scale table
+// serves both halves: scale[p] holds w^brev(p) / n for p < n/2 (the 1/2 included) and inc w^brev(p - n/2) / n above
+// (the join's factor inc included).  tw[e] = w^e, e < n/2, of the FULL domain in both kernels.
+static __global__ void ntt_split_kernel(fe_t* __restrict__ a, uint32_t half, int parity, const fe_t* __restrict__ tw) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= half) return;
+    fe_t lo = ld_fe(a + i), hi = ld_fe(a + i + half);
+    if (!parity) {
+        st_fe(a + i, Fr::add(lo, hi));
+        return;
+    }
+    fe_t d = Fr::sub(lo, hi);
+    if (i) d = Fr::neg(Fr::mul(d, ldg_fe(tw + (half - i))));   // w^(-i) = -w^(n/2 - i)
+    st_fe(a + i, d);
+}
+
+// P[lo + i] = from_montgomery(XA XB - XC), X = E[i] + w^(lo + i) O[i]; E/O: this range's slices of the two half transforms
+static __global__ void ntt_join_halves_kernel(const fe_t* __restrict__ eA, const fe_t* __restrict__ oA,
+                                              const fe_t* __restrict__ eB, const fe_t* __restrict__ oB,
+                                              const fe_t* __restrict__ eC, const fe_t* __restrict__ oC,
+                                              fe_t* __restrict__ P, uint32_t count, uint32_t lo, uint32_t half,
+                                              const fe_t* __restrict__ tw) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint32_t k = lo + i;
+    fe_t w = ldg_fe(tw + (k >= half ? k - half : k));
+    if (k >= half) w = Fr::neg(w);
+    fe_t xa = Fr::add(ld_fe(eA + i), Fr::mul(w, ld_fe(oA + i)));
+    fe_t xb = Fr::add(ld_fe(eB + i), Fr::mul(w, ld_fe(oB + i)));
+    fe_t xc = Fr::add(ld_fe(eC + i), Fr::mul(w, ld_fe(oC + i)));
+    st_fe(P + i, Fr::from_mont(Fr::sub(Fr::mul(xa, xb), xc)));
+}
+
 inline std::vector<int> ntt_plan(int logn) {
     int np = (logn + NTT_TILE_LOG - 1) / NTT_TILE_LOG;
     if (np < 1) np = 1;
@@ -293,7 +330,7 @@ struct NttDomain {
         return w;  // Montgomery form
     }
 
-    void init(int logn_, cudaStream_t s) {
+    void init(int logn_, cudaStream_t s, bool with_scale = true) {   // with_scale false: tw only (the half domain)
         using namespace g16h;
         logn = logn_;
         if (logn < 1 || logn > 28) throw std::runtime_error("NTT domain must be 2^1 .. 2^28");
@@ -304,7 +341,7 @@ struct NttDomain {
                                       (int)ntt_pass_smem(NTT_TILE_LOG)));
         size_t n = size_t(1) << logn;
         tw.alloc((n / 2 ? n / 2 : 1) * sizeof(fe_t));
-        scale.alloc(n * sizeof(fe_t));
+        if (with_scale) scale.alloc(n * sizeof(fe_t));
         U256 w = root_of_unity(logn);
         // row a6: inc = w[logn + 1]; for logn == 28 ffjavascript uses Fr.shift = nqr^2 = 25
         U256 inc = logn < 28 ? root_of_unity(logn + 1) : HFr::from_u64(25);
@@ -326,8 +363,9 @@ struct NttDomain {
         std::memcpy(&ninv_m, ninv.v, 32);
         uint32_t half = (uint32_t)(n / 2 ? n / 2 : 1);
         ntt_powers_kernel<<<(half + 255) / 256, 256, 0, s>>>(tw.as<fe_t>(), half, logn - 1, false, dpw.as<fe_t>(), one_m);
-        ntt_powers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scale.as<fe_t>(), (uint32_t)n, logn, true,
-                                                                      dpw.as<fe_t>() + 32, ninv_m);
+        if (with_scale)
+            ntt_powers_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(scale.as<fe_t>(), (uint32_t)n, logn, true,
+                                                                          dpw.as<fe_t>() + 32, ninv_m);
         G16_CUDA(cudaGetLastError());
         G16_CUDA(cudaStreamSynchronize(s));
     }
@@ -359,6 +397,15 @@ struct NttDomain {
         for (size_t i = 0; i < ks.size(); i++) {
             sl -= ks[i];
             pass<true, true>(a, sl, ks[i], (with_scale && sl == 0) ? scale.as<fe_t>() : nullptr, s);
+        }
+    }
+    // inverse transform whose last pass multiplies by a caller's table (bit-reversed positions)
+    void inverse_dif_with(fe_t* a, const fe_t* sc, cudaStream_t s) const {
+        std::vector<int> ks = ntt_plan(logn);
+        int sl = logn;
+        for (size_t i = 0; i < ks.size(); i++) {
+            sl -= ks[i];
+            pass<true, true>(a, sl, ks[i], sl == 0 ? sc : nullptr, s);
         }
     }
     void forward_dit(fe_t* a, cudaStream_t s) const {

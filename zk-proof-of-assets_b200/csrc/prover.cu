@@ -185,6 +185,7 @@ struct g16_zkey {
     std::vector<uint8_t> next_public;
     DevBuf pa, pb, pc;         // A, B, C evaluations; pa ends up holding the H scalars
     NttDomain dom;
+    NttDomain dom_half;                // 2^(logn-1) points, twiddles only: g16_h_transform_half (built on first use)
     cudaStream_t s_main = nullptr, s_msm[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     HPoint<HFq> fin_a, fin_b1, fin_c;   // finished witness MSMs of the last prove_device
     HPoint<HFq2> fin_b2;
@@ -564,6 +565,8 @@ static void enqueue_h_pipeline(g16_zkey* zk) {
 // H.n elements each; the join (row a8) then runs on the range only
 struct JoinedSlices {
     const fe_t *a, *b, *c;
+    // transforms split in halves (g16_h_transform_half): a, b, c = the even-coefficient halves' slices, these the odd ones
+    const fe_t *oa = nullptr, *ob = nullptr, *oc = nullptr;
 };
 
 // the device part of a proof: five partial MSM sums of this shard, left in the Msm objects' host buffers.
@@ -632,7 +635,13 @@ static void prove_device(g16_zkey* zk, const JoinedSlices* js = nullptr, bool on
             // fall through to the witness MSMs below
         } else if (js) {
             G16_CUDA(cudaEventRecord(zk->ev[1], zk->s_main));
-            if (zk->H.n) {
+            if (zk->H.n && js->oa) {
+                ntt_join_halves_kernel<<<(unsigned)((zk->H.n + 255) / 256), 256, 0, zk->s_main>>>(
+                    js->a, js->oa, js->b, js->ob, js->c, js->oc, zk->pa.as<fe_t>() + zk->H.lo, (uint32_t)zk->H.n,
+                    (uint32_t)zk->H.lo, zk->domain_size / 2, zk->dom.tw.as<fe_t>());
+                G16_CUDA(cudaGetLastError());
+                G16_LAUNCHED(1);
+            } else if (zk->H.n) {
                 ntt_join_kernel<<<(unsigned)((zk->H.n + 255) / 256), 256, 0, zk->s_main>>>(
                     js->a, js->b, js->c, zk->pa.as<fe_t>() + zk->H.lo, (uint32_t)zk->H.n);
                 G16_CUDA(cudaGetLastError());
@@ -999,6 +1008,57 @@ int g16_h_transform(g16_zkey* zk, int which) {
         float ms = 0;
         cudaEventElapsedTime(&ms, t0, zk->ev[1]); zk->t_transform_ms[0] = ms;
         cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_transform_ms[1] = ms;
+        return (int)G16_OK;
+    });
+}
+
+int g16_h_transform_half(g16_zkey* zk, int poly, int parity) {
+    return guarded([&]() {
+        if (!zk || poly < 0 || poly > 2 || (parity & ~1)) return fail(G16_ERR_GENERIC, "bad argument");
+        if (!zk->witness_loaded) return fail(G16_ERR_GENERIC, "no witness loaded");
+        if (zk->logn < 2) return fail(G16_ERR_GENERIC, "a split transform needs a domain of at least 4 points");
+        G16_CUDA(cudaSetDevice(zk->device));
+        cudaStream_t s = zk->s_main;
+        uint32_t n = zk->domain_size, half = n / 2;
+        if (zk->dom_half.logn != zk->logn - 1) zk->dom_half.init(zk->logn - 1, s, false);   // first call only (allocates)
+        if (!zk->witness_enqueued) G16_CUDA(cudaEventRecord(zk->ev[0], s));
+        cudaEvent_t t0 = zk->ev[15];
+        G16_CUDA(cudaEventRecord(t0, s));
+        r1cs_eval_kernel<<<(n + 127) / 128, 128, 0, s>>>(zk->row_ptr.as<uint32_t>(), zk->col.as<uint32_t>(),
+                                                         zk->val.as<fe_t>(), zk->w.as<fe_t>(), n, zk->pa.as<fe_t>(),
+                                                         zk->pb.as<fe_t>(), zk->pc.as<fe_t>());
+        G16_CUDA(cudaGetLastError());
+        G16_CUDA(cudaEventRecord(zk->ev[1], s));
+        fe_t* a = poly == 0 ? zk->pa.as<fe_t>() : poly == 1 ? zk->pb.as<fe_t>() : zk->pc.as<fe_t>();
+        ntt_split_kernel<<<(half + 255) / 256, 256, 0, s>>>(a, half, parity, zk->dom.tw.as<fe_t>());
+        G16_CUDA(cudaGetLastError());
+        zk->dom_half.inverse_dif_with(a, zk->dom.scale.as<fe_t>() + size_t(parity) * half, s);
+        zk->dom_half.forward_dit(a, s);
+        G16_CUDA(cudaGetLastError());
+        // the half twice, so that any range [lo, lo + count) of the buffer reads Y[k mod n/2]: slices cut like a whole transform's
+        G16_CUDA(cudaMemcpyAsync(a + half, a, size_t(half) * sizeof(fe_t), cudaMemcpyDeviceToDevice, s));
+        G16_LAUNCHED(2 + 2 * ntt_plan(zk->logn - 1).size());
+        G16_CUDA(cudaEventRecord(zk->ev[2], s));
+        G16_CUDA(cudaStreamSynchronize(s));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, t0, zk->ev[1]); zk->t_transform_ms[0] = ms;
+        cudaEventElapsedTime(&ms, zk->ev[1], zk->ev[2]); zk->t_transform_ms[1] = ms;
+        return (int)G16_OK;
+    });
+}
+
+int g16_prove_partial_joined_halves(g16_zkey* zk, const void* const d_halves[6], uint8_t* partial_out) {
+    return guarded([&]() {
+        if (!zk || !partial_out || !d_halves) return fail(G16_ERR_GENERIC, "null argument");
+        for (int i = 0; i < 6; i++)
+            if (zk->H.n && !d_halves[i]) return fail(G16_ERR_GENERIC, "null argument");
+        JoinedSlices js{(const fe_t*)d_halves[0], (const fe_t*)d_halves[2], (const fe_t*)d_halves[4],
+                        (const fe_t*)d_halves[1], (const fe_t*)d_halves[3], (const fe_t*)d_halves[5]};
+        if (!zk->H.n) js.oa = nullptr;
+        prove_device(zk, &js);
+        zk->t_ms[1] = zk->t_transform_ms[0];
+        zk->t_ms[2] += zk->t_transform_ms[1];
+        export_partial(zk, partial_out);
         return (int)G16_OK;
     });
 }
