@@ -252,6 +252,11 @@ int g16_zkey_beacon(const char* zkey_in, const char* zkey_out, const char* name,
 int g16_zkey_export_vkey(const char* zkey_path, char* out, size_t* out_len);
 /* test hook: which = 0 Blake2b-512 (64 bytes out), 1 SHA-256 (32 bytes out) */
 int g16_test_hash(int which, const uint8_t* data, size_t n, uint8_t* out);
+/* Test hook: the entry count, window bits, window count and sort path an MSM of n points would use, and the limits
+ * enforced when its workspace is reserved (32-bit entry positions, 31-bit base indices, cub's int item count on the
+ * radix-sort path): G16_ERR_GENERIC with "... shard it" in g16_last_error beyond them.  Host arithmetic only; works
+ * without a GPU.  c = 0 picks the window width from n as a proof would. */
+int g16_test_msm_shape(uint64_t n, int c, int table, int sparse, uint64_t* entries, int* c_out, int* windows, int* dense);
 
 #ifdef __cplusplus
 }

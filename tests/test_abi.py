@@ -81,3 +81,40 @@ def test_cli_argv_contract():
     assert p.returncode != 0 and "Usage: prover <circuit.zkey> <witness.wtns> <proof.json> <public.json>" in p.stderr
     p = subprocess.run([exe, "/nonexistent.zkey", "/nonexistent.wtns", "/tmp/p.json", "/tmp/u.json"], capture_output=True, text=True)
     assert p.returncode != 0 and p.stderr.strip()
+
+
+def test_msm_index_limits_are_enforced_before_any_sort():
+    """Msm::reserve's limit arithmetic (host only): entry positions are 32-bit, base indices 31-bit, and cub's radix sort
+    on the dense path takes an int item count -- a count above INT_MAX would come back from cub unsorted, i.e. a silently
+    wrong proof.  Every case beyond a limit must be refused with 'shard it', every BASELINE shape must pass."""
+    pkg = load_pkg()
+    INT_MAX = (1 << 31) - 1
+    # the reference's shapes: H MSM over a window table (dense scalars) at 2^21 .. 2^26
+    for logn in (21, 24, 25, 26):
+        sh = pkg.msm_shape(1 << logn, table=True)
+        assert sh["entries"] == (1 << logn) * sh["windows"] <= INT_MAX
+        assert sh["dense"] == (sh["entries"] > 80 << 20)
+    assert not pkg.msm_shape(1 << 21, table=True)["dense"] and pkg.msm_shape(1 << 24, table=True)["dense"]
+    # witness MSMs (sparse scalars, no table) never take the radix path
+    assert not pkg.msm_shape(1 << 26, sparse=True)["dense"]
+    # 2^28 points, dense over a table: c = 20 -> 13 windows -> 3.5e9 entries: above INT_MAX and above 2^31 - 1 base slots
+    with pytest.raises(pkg.G16Error) as e:
+        pkg.msm_shape(1 << 28, c=20, table=True)
+    assert "shard it" in e.value.message
+    # the exact boundary of the radix path's int count: n * windows just below / above INT_MAX (c = 16 -> 16 windows)
+    w = pkg.msm_shape(1 << 20, c=16, table=True)["windows"]
+    ok_n = INT_MAX // w
+    assert pkg.msm_shape(ok_n, c=16, table=True)["entries"] == ok_n * w
+    with pytest.raises(pkg.G16Error):
+        pkg.msm_shape(ok_n + 1, c=16, table=True)
+    # without a table (counting sort): 32-bit entry positions are the limit
+    w = pkg.msm_shape(1 << 20, c=16)["windows"]
+    ok_n = ((1 << 32) - 1) // w
+    assert pkg.msm_shape(ok_n, c=16)["entries"] < 1 << 32
+    with pytest.raises(pkg.G16Error) as e:
+        pkg.msm_shape(ok_n + 1, c=16)
+    assert "32-bit entry indices" in e.value.message
+    # base indices carry the digit's sign in bit 31
+    with pytest.raises(pkg.G16Error) as e:
+        pkg.msm_shape(1 << 31, c=24)
+    assert "31-bit base indices" in e.value.message

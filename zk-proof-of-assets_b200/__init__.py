@@ -44,7 +44,7 @@ ABI_SYMBOLS = [
     "g16_prove_partial_joined", "g16_prove_begin", "g16_h_transform_half", "g16_prove_partial_joined_halves", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
     "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files", "g16_merkle_root_static",
-    "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash",
+    "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash", "g16_test_msm_shape",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -123,6 +123,7 @@ def lib():
         L.g16_h_buffer.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_prove_partial_joined.argtypes = [ctypes.c_void_p] * 5
         L.g16_prove_begin.argtypes = [ctypes.c_void_p]
+        L.g16_test_msm_shape.argtypes = [ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 4
         L.g16_h_transform_half.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
         L.g16_prove_partial_joined_halves.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_sanitize.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_char_p,
@@ -580,6 +581,14 @@ def merkle_files(anon_set_csv, poa_input_json, output_dir, device=-1):
     o = make_opts(device=device)
     _check(lib().g16_merkle_files(os.fsencode(anon_set_csv), os.fsencode(poa_input_json) if poa_input_json else None,
                                   os.fsencode(output_dir), ctypes.byref(o)))
+
+
+def msm_shape(n, c=0, table=False, sparse=False):
+    """test hook (host arithmetic, no GPU needed): {entries, c, windows, dense} of an MSM of n points, or G16Error beyond
+    the index limits Msm::reserve enforces"""
+    e, co, w, d = ctypes.c_uint64(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _check(lib().g16_test_msm_shape(n, c, int(table), int(sparse), ctypes.byref(e), ctypes.byref(co), ctypes.byref(w), ctypes.byref(d)))
+    return {"entries": e.value, "c": co.value, "windows": w.value, "dense": bool(d.value)}
 
 
 MERKLE_STATIC_MAX_ROWS = 65536

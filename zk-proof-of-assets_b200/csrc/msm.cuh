@@ -663,6 +663,45 @@ struct MsmConfig {
     bool table = false; // fixed-base window table (build_table() before the first run)
 };
 
+// The sizes reserve() derives from (n, config), and the limits it enforces -- host arithmetic only, no CUDA call, so that
+// the limits can be tested without a device (g16_test_msm_shape).  Entry positions and counters are 32-bit, base indices
+// 31-bit (the top bit carries the sign of the digit), and cub's radix sort (the dense path) takes an int item count.
+struct MsmShape {
+    int c = 0, Wd = 0, W = 0;
+    uint32_t bpw = 0, nb = 0;
+    size_t m_max = 0;      // digits an MSM of this shape can produce = entries to sort
+    bool dense = false;    // fixed-slot digits + radix sort (see Msm::dense)
+};
+inline size_t msm_dense_min() {
+    static size_t v = [] { const char* e = std::getenv("G16_DENSE_MIN"); return e ? size_t(std::atoll(e)) : size_t(80) << 20; }();
+    return v;
+}
+inline MsmShape msm_shape(size_t n, const MsmConfig& cfg) {
+    MsmShape sh;
+    int c = cfg.c ? cfg.c
+          : cfg.table ? (cfg.sparse ? msm_pick_c_table_sparse(n) : msm_pick_c_table(n))
+          : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
+    if (c < 2) c = 2;
+    if (c > 24) c = 24;
+    if (cfg.table && c < 6) c = 6;
+    sh.c = c;
+    sh.Wd = msm_num_windows(c);
+    sh.W = cfg.table ? 1 : sh.Wd;
+    if (size_t(sh.W) > 256) throw std::runtime_error("MSM: too many windows");
+    sh.bpw = 1u << (c - 1);
+    sh.nb = uint32_t(sh.W) * sh.bpw;
+    if (n > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM too large for 31-bit base indices; shard it");
+    sh.m_max = n * size_t(sh.Wd);
+    if (sh.m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
+    if (cfg.table && sh.m_max > size_t(MSM_INDEX_MASK))
+        throw std::runtime_error("MSM window table too large for 31-bit base indices; shard it");
+    sh.dense = cfg.table && !cfg.sparse && sh.m_max > msm_dense_min();
+    if (sh.dense && sh.m_max > size_t(INT_MAX))
+        throw std::runtime_error("MSM too large for the radix sort's int item count; shard it");
+    // cub's scans take int item counts as well: nb + 1 <= 11 * 2^23 + 1 (c <= 24), far below INT_MAX
+    return sh;
+}
+
 // Counters a finished MSM leaves behind (for bench.py's work model and tests)
 struct MsmStats {
     unsigned long long entries = 0;  // non-zero digits = mixed additions issued
@@ -797,10 +836,7 @@ private:
     // counting sort's scattered stores no longer stay in L2 (measured: 27 M entries 0.48 ms counting / 0.87 ms radix,
     // 201 M entries 8.0 ms / 6.0 ms)
     bool dense() const { return cfg.table && !cfg.sparse && cap_n * size_t(Wd) > dense_min(); }
-    static size_t dense_min() {
-        static size_t v = [] { const char* e = std::getenv("G16_DENSE_MIN"); return e ? size_t(std::atoll(e)) : size_t(80) << 20; }();
-        return v;
-    }
+    static size_t dense_min() { return msm_dense_min(); }
 };
 
 #ifdef G16_MSM_INSTANTIATE
@@ -809,22 +845,13 @@ template <class C>
 void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     cfg = cfg_in;
     cap_n = n;
-    c = cfg.c ? cfg.c
-        : cfg.table ? (cfg.sparse ? msm_pick_c_table_sparse(n) : msm_pick_c_table(n))
-        : cfg.sparse ? msm_pick_c_sparse(n) : msm_pick_c(n);
-    if (c < 2) c = 2;
-    if (c > 24) c = 24;
-    if (cfg.table && c < 6) c = 6;
-    Wd = msm_num_windows(c);
-    W = cfg.table ? 1 : Wd;
-    if (size_t(W) > 256) throw std::runtime_error("MSM: too many windows");
-    bpw = 1u << (c - 1);
-    nb = uint32_t(W) * bpw;
-    size_t m_max = n * size_t(Wd);
-    // entry positions and counters are 32-bit; cub's scans take int item counts (nb + 1 <= 2^31 always holds here)
-    if (m_max >= (size_t(1) << 32)) throw std::runtime_error("MSM too large for 32-bit entry indices; shard it");
-    if (cfg.table && m_max > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM window table too large for 31-bit base indices; shard it");
-    if (n > size_t(MSM_INDEX_MASK)) throw std::runtime_error("MSM too large for 31-bit base indices; shard it");
+    const MsmShape sh = msm_shape(n, cfg);   // throws beyond the index limits ("shard it")
+    c = sh.c;
+    Wd = sh.Wd;
+    W = sh.W;
+    bpw = sh.bpw;
+    nb = sh.nb;
+    size_t m_max = sh.m_max;
     if (cfg.T > T_MAX) cfg.T = T_MAX;
     // level-0 chunks: 16 buckets when there are enough buckets to fill the machine with chunk threads, else 8
     // (half the dependency chain); level 1 works on bpw/L points only, so its chunks are short (latency, not work)
@@ -848,7 +875,6 @@ void Msm<C>::reserve(size_t n, const MsmConfig& cfg_in) {
     vals.alloc(e * 4);
     size_t t1 = 0;
     if (dense()) {
-        if (m_max > size_t(INT_MAX)) throw std::runtime_error("MSM too large for the radix sort's int item count; shard it");
         keys_a.alloc(e * 4); keys_b.alloc(e * 4); vals_b.alloc(e * 4);
         cub::DoubleBuffer<uint32_t> dk(keys_a.as<uint32_t>(), keys_b.as<uint32_t>());
         cub::DoubleBuffer<uint32_t> dv(vals.as<uint32_t>(), vals_b.as<uint32_t>());

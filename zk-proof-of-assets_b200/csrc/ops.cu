@@ -336,6 +336,23 @@ int g16_msm_create(int is_g2, size_t max_n, const g16_opts* opts, g16_msm** out)
 
 void g16_msm_destroy(g16_msm* m) { delete m; }
 
+// test hook: the sizes and limits Msm::reserve derives from (n, window bits, table, sparse) -- host arithmetic only, works
+// without a device.  G16_ERR_GENERIC + message ("... shard it") beyond the 32-bit entry / 31-bit base index / int item limits.
+int g16_test_msm_shape(uint64_t n, int c, int table, int sparse, uint64_t* entries, int* c_out, int* windows, int* dense) {
+    return guarded([&]() {
+        MsmConfig cfg;
+        cfg.c = c;
+        cfg.table = table != 0;
+        cfg.sparse = sparse != 0;
+        MsmShape sh = msm_shape(size_t(n), cfg);
+        if (entries) *entries = sh.m_max;
+        if (c_out) *c_out = sh.c;
+        if (windows) *windows = sh.Wd;
+        if (dense) *dense = sh.dense ? 1 : 0;
+        return (int)G16_OK;
+    });
+}
+
 int g16_msm_run_dev(g16_msm* m, const void* d_bases, const void* d_scalars, size_t n, uint8_t* out_affine) {
     return guarded([&]() {
         if (!m || !out_affine) return fail(G16_ERR_GENERIC, "null argument");
