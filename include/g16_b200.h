@@ -242,6 +242,16 @@ int g16_merkle_root_static(const void* d_rows, size_t n_rows, void* d_root, void
  * specification); acceptance of that record by `snarkjs zkey verify` is unverified on this box (no node).
  * entropy may be NULL (64 bytes are drawn with getrandom(2)).  contribution_hash (optional) receives the Blake2b-512
  * hash snarkjs prints as "Contribution Hash". */
+/* `snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>` (`groth16 setup`, scripts/g16_setup.sh:240-252):
+ * the whole proving key -- header, IC, coefficients (x R^2), A, B1, B2, C, H, empty contributions section with the
+ * circuit hash -- from a circuit and a ceremony file PREPARED FOR PHASE 2 (sections 12-15, as `snarkjs powersoftau
+ * prepare phase2` writes them); gamma = delta = 1.  The sparse linear combinations of the ceremony's Lagrange points run
+ * on the GPU (csrc/zkey_new.cu); only the needed ranges of the ceremony file are read.  cs_hash_out (optional) receives
+ * the circuit hash (UNPINNED: restated from the published source, no zkey in the reference to pin it on).  Errors:
+ * G16_ERR_CURVE for a circuit or ceremony over another field, G16_ERR_GENERIC "circuit too big for this power of tau
+ * ceremony", G16_ERR_FORMAT for malformed files or a ceremony file that is not prepared. */
+int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const char* zkey_out, const g16_opts* opts,
+                 uint8_t cs_hash_out[64]);
 int g16_zkey_contribute(const char* zkey_in, const char* zkey_out, const char* name, const uint8_t* entropy, size_t entropy_len,
                         const g16_opts* opts, uint8_t contribution_hash[64]);
 /* delta' from 2^num_iterations_exp iterations of SHA-256 over beacon_hash (scripts/g16_setup.sh:272-277) */

@@ -44,7 +44,7 @@ ABI_SYMBOLS = [
     "g16_prove_partial_joined", "g16_prove_begin", "g16_h_transform_half", "g16_prove_partial_joined_halves", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
     "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files", "g16_merkle_root_static",
-    "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash", "g16_test_msm_shape",
+    "g16_zkey_new", "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash", "g16_test_msm_shape",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -141,6 +141,7 @@ def lib():
         L.g16_merkle_find.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_uint64, ctypes.c_void_p]
         L.g16_merkle_files.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
         L.g16_merkle_root_static.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_new.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_zkey_contribute.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
                                           ctypes.c_void_p, ctypes.c_void_p]
         L.g16_zkey_beacon.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
@@ -603,6 +604,15 @@ def merkle_root_static(d_rows, n_rows, d_root, stream=None):
 
 
 # ---- phase-2 ceremony steps + vkey export (scripts/g16_setup.sh:254-295) ------------------------------------------
+def zkey_new(r1cs_path, ptau_path, zkey_out, device=-1):
+    """`snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <out.zkey>` (`groth16 setup`, scripts/g16_setup.sh:240-252); the
+    sparse combinations of the ceremony's Lagrange points run on the GPU.  -> circuit hash"""
+    o = make_opts(device=device)
+    h = ctypes.create_string_buffer(64)
+    _check(lib().g16_zkey_new(os.fsencode(r1cs_path), os.fsencode(ptau_path), os.fsencode(zkey_out), ctypes.byref(o), h))
+    return h.raw
+
+
 def zkey_contribute(zkey_in, zkey_out, name="", entropy=None, device=-1):
     """`snarkjs zkey contribute <in> <out> --name=.. -e=..`; sections 8/9 are updated on the GPU.  -> contribution hash"""
     o = make_opts(device=device)

@@ -15,7 +15,8 @@
 //                                   the limb file scripts/sanitize_groth16_proof.py:112-123 writes, byte for byte
 // Anonymity-set Merkle tree (the argv of the reference's `merkle-tree`, scripts/merkle_tree.rs:29-44):
 //     prover --merkle-tree --anon-set <csv> --poa-input-data <json> --output-dir <dir>
-// Setup steps (snarkjs' argument order, scripts/g16_setup.sh:254-295):
+// Setup steps (snarkjs' argument order, scripts/g16_setup.sh:240-295):
+//     prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>
 //     prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
 //     prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]
 //     prover --zkey-export-vkey <zkey> <verification_key.json>
@@ -142,7 +143,8 @@ static int merkle_cli(int argc, char** argv) {
     return 0;
 }
 
-// the setup steps of scripts/g16_setup.sh:254-295 with snarkjs' argument order:
+// the setup steps of scripts/g16_setup.sh:240-295 with snarkjs' argument order:
+//   prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>
 //   prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
 //   prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]
 //   prover --zkey-export-vkey <zkey> <verification_key.json>
@@ -166,7 +168,10 @@ static int setup_cli(int argc, char** argv) {
     };
     uint8_t h[64];
     int rc;
-    if (cmd == "--zkey-contribute" && pos.size() == 2) {
+    if (cmd == "--zkey-new" && pos.size() == 3) {
+        rc = g16_zkey_new(pos[0].c_str(), pos[1].c_str(), pos[2].c_str(), nullptr, h);
+        if (rc == G16_OK) std::printf("Circuit Hash: \n\t\t%s\n", hex(h).c_str());
+    } else if (cmd == "--zkey-contribute" && pos.size() == 2) {
         rc = g16_zkey_contribute(pos[0].c_str(), pos[1].c_str(), name.c_str(), has_entropy ? (const uint8_t*)entropy.data() : nullptr,
                                  entropy.size(), nullptr, h);
         if (rc == G16_OK) std::printf("Contribution Hash: \n\t\t%s\n", hex(h).c_str());
@@ -192,7 +197,8 @@ static int setup_cli(int argc, char** argv) {
             }
         }
     } else {
-        std::fprintf(stderr, "Usage: prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]\n"
+        std::fprintf(stderr, "Usage: prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>\n"
+                             "       prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]\n"
                              "       prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]\n"
                              "       prover --zkey-export-vkey <zkey> <verification_key.json>\n");
         return 2;
