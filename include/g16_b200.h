@@ -242,7 +242,7 @@ int g16_merkle_root_static(const void* d_rows, size_t n_rows, void* d_root, void
  * specification); acceptance of that record by `snarkjs zkey verify` is unverified on this box (no node).
  * entropy may be NULL (64 bytes are drawn with getrandom(2)).  contribution_hash (optional) receives the Blake2b-512
  * hash snarkjs prints as "Contribution Hash". */
-/* `snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>` (`groth16 setup`, scripts/g16_setup.sh:240-252):
+/* `snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>` (`groth16 setup`, scripts/g16_setup.sh:239-254):
  * the whole proving key -- header, IC, coefficients (x R^2), A, B1, B2, C, H, empty contributions section with the
  * circuit hash -- from a circuit and a ceremony file PREPARED FOR PHASE 2 (sections 12-15, as `snarkjs powersoftau
  * prepare phase2` writes them); gamma = delta = 1.  The sparse linear combinations of the ceremony's Lagrange points run

@@ -27,6 +27,11 @@ int g16_synth_write(g16_synth* s, uint8_t* zkey_out, uint8_t* wtns_out);
 int g16_synth_expected(g16_synth* s, const uint8_t r[32], const uint8_t sblind[32], uint8_t out[256]);
 /* verification key points, standard form LE: alpha1(64) beta2(128) gamma2(128) delta2(128) IC[(nPublic+1)](64 each) */
 int g16_synth_vkey(g16_synth* s, uint8_t* out);
+/* the circuit as an .r1cs file plus a powers-of-tau file under the generator's tau, alpha, beta: the inputs of `zkey new`
+ * (g16_zkey_new).  The ceremony file (power = log2(domain) + 1, iden3 layout) is SPARSE: only the ranges `zkey new` reads
+ * for this circuit hold points.  Sections 4-7 of the resulting key equal g16_synth_write's (they do not depend on gamma,
+ * delta); IC, C and H differ by the factors 1/gamma, 1/delta that `zkey new` fixes at 1. */
+int g16_synth_write_setup_inputs(g16_synth* s, const char* r1cs_path, const char* ptau_path);
 /* k*G for n standard-form scalars; out = zkey records (Montgomery affine, all-zero = infinity) */
 int g16_synth_fixed_base(int is_g2, const uint8_t* scalars, size_t n, uint8_t* out);
 const char* g16_synth_last_error(void);

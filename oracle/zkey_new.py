@@ -1,7 +1,7 @@
 """`snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>` -- oracle for SURVEY.md 8(f) rank 2 (the first setup step).
 
 ORACLE CODE: TEST INFRASTRUCTURE.  CPU restatement (Python big-int group arithmetic, no trapdoor) of what the reference
-runs in scripts/g16_setup.sh:240-252 (`snarkjs groth16 setup` = zkey new) on the files scripts/g16_setup.sh:196-237
+runs in scripts/g16_setup.sh:239-254 (`snarkjs groth16 setup` = zkey new) on the files scripts/g16_setup.sh:196-237
 names.  snarkjs 0.7.2 is not under /root/reference (pnpm-lock.yaml:2231-2244) and cannot run here, so this follows its
 published algorithm (src/zkey_new.js, r1csfile 0.0.47 readR1cs, src/powersoftau_utils.js, powersoftau_preparephase2.js):
   .r1cs v1 : sec1 { u32 n8 | prime | u32 nWires | nPubOut | nPubIn | nPrvIn | u64 nLabels | u32 nConstraints }

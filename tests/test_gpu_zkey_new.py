@@ -44,7 +44,7 @@ def test_zkey_new_matches_the_oracle_byte_for_byte(pkg, small, power):
 
 
 def test_new_key_goes_through_contribute_export_prove_verify(pkg, small):
-    """the reference's sequence (scripts/g16_setup.sh:240-295, g16_prove.sh, g16_verify.sh) on one library"""
+    """the reference's sequence (scripts/g16_setup.sh:239-295, g16_prove.sh, g16_verify.sh) on one library"""
     d, circ = small["dir"], small["circ"]
     pkg.zkey_new(d / "c.r1cs", d / "pot8.ptau", d / "k0.zkey")
     pkg.zkey_contribute(d / "k0.zkey", d / "k1.zkey", name="first", entropy="abc")
@@ -110,3 +110,35 @@ def test_zkey_new_refusals_and_cli(pkg, small, tmp_path):
     assert (tmp_path / "cli.zkey").read_bytes() == ZN.zkey_new((d / "c.r1cs").read_bytes(), raw)
     r = subprocess.run([exe, "--zkey-new", str(d / "c.r1cs")], capture_output=True, text=True)
     assert r.returncode == 2
+
+
+@pytest.mark.parametrize("n_vars,n_public,n_cons", [(30000, 1, 32000), (2083343, 1, 2094670)])
+def test_zkey_new_at_scale_agrees_with_the_fixture_generator_and_proves(pkg, tmp_path, n_vars, n_public, n_cons):
+    """2^15, and BASELINE's c2-layer-one shape (2^21): sections 4-7 of the new key equal the known-trapdoor generator's
+    (they do not depend on gamma, delta), and a proof made with the new key verifies against its exported vkey -- which
+    pins IC, C and H (a wrong point in any of them breaks the pairing equation)."""
+    import time
+    sy = pkg.Synth(n_vars, n_public, n_cons, 11, 12)
+    sy.write_setup_inputs(tmp_path / "c.r1cs", tmp_path / "pot.ptau")
+    t0 = time.perf_counter()
+    pkg.zkey_new(tmp_path / "c.r1cs", tmp_path / "pot.ptau", tmp_path / "new.zkey")
+    dt = time.perf_counter() - t0
+    ref, wtns = sy.write()
+    ref = bytes(ref)
+    got = (tmp_path / "new.zkey").read_bytes()
+    _, sa = binfile.read_binfile(got, b"zkey")
+    _, sb = binfile.read_binfile(ref, b"zkey")
+    for t in (1, 4, 5, 6, 7):
+        (pa, la), (pb, lb) = sa[t][0], sb[t][0]
+        assert la == lb and got[pa:pa + la] == ref[pb:pb + lb], t
+    for t in (3, 8, 9):
+        assert sa[t][0][1] == sb[t][0][1]
+    vkey = pkg.zkey_export_vkey(tmp_path / "new.zkey")
+    with pkg.ZKey(got) as zk:
+        proof, public = zk.prove(wtns)
+    assert pkg.verify(vkey, public, proof)
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "zkey_new_%d.json" % n_cons), "w") as f:
+            json.dump({"n_vars": n_vars, "n_public": n_public, "n_constraints": n_cons, "zkey_new_wall_s": dt,
+                       "zkey_bytes": len(got)}, f)

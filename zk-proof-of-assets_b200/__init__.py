@@ -48,7 +48,7 @@ ABI_SYMBOLS = [
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
-    "g16_synth_vkey", "g16_synth_fixed_base", "g16_synth_last_error",
+    "g16_synth_vkey", "g16_synth_fixed_base", "g16_synth_last_error", "g16_synth_write_setup_inputs",
 ]
 
 
@@ -167,6 +167,7 @@ def synth_lib():
         S.g16_synth_write.argtypes = [ctypes.c_void_p] * 3
         S.g16_synth_expected.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
         S.g16_synth_vkey.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        S.g16_synth_write_setup_inputs.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_char_p]
         S.g16_synth_fixed_base.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p]
         _synth = S
     return _synth
@@ -605,7 +606,7 @@ def merkle_root_static(d_rows, n_rows, d_root, stream=None):
 
 # ---- phase-2 ceremony steps + vkey export (scripts/g16_setup.sh:254-295) ------------------------------------------
 def zkey_new(r1cs_path, ptau_path, zkey_out, device=-1):
-    """`snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <out.zkey>` (`groth16 setup`, scripts/g16_setup.sh:240-252); the
+    """`snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <out.zkey>` (`groth16 setup`, scripts/g16_setup.sh:239-254); the
     sparse combinations of the ceremony's Lagrange points run on the GPU.  -> circuit hash"""
     o = make_opts(device=device)
     h = ctypes.create_string_buffer(64)
@@ -674,6 +675,11 @@ class Synth:
         if S.g16_synth_write(self._h, _addr(zk) if zk is not None else None, _addr(wt) if wt is not None else None):
             raise RuntimeError(S.g16_synth_last_error().decode())
         return zk, wt
+
+    def write_setup_inputs(self, r1cs_path, ptau_path):
+        """the circuit as .r1cs + a (sparse) powers-of-tau file under this generator's tau, alpha, beta: `zkey new`'s inputs"""
+        if synth_lib().g16_synth_write_setup_inputs(self._h, os.fsencode(r1cs_path), os.fsencode(ptau_path)):
+            raise RuntimeError(synth_lib().g16_synth_last_error().decode())
 
     def expected(self, r, s):
         """closed-form proof for pinned r,s -> (pi_a (x,y), pi_b ((x0,x1),(y0,y1)), pi_c (x,y)) as ints"""

@@ -15,7 +15,7 @@
 //                                   the limb file scripts/sanitize_groth16_proof.py:112-123 writes, byte for byte
 // Anonymity-set Merkle tree (the argv of the reference's `merkle-tree`, scripts/merkle_tree.rs:29-44):
 //     prover --merkle-tree --anon-set <csv> --poa-input-data <json> --output-dir <dir>
-// Setup steps (snarkjs' argument order, scripts/g16_setup.sh:240-295):
+// Setup steps (snarkjs' argument order, scripts/g16_setup.sh:239-295):
 //     prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>
 //     prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
 //     prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]
@@ -143,7 +143,7 @@ static int merkle_cli(int argc, char** argv) {
     return 0;
 }
 
-// the setup steps of scripts/g16_setup.sh:240-295 with snarkjs' argument order:
+// the setup steps of scripts/g16_setup.sh:239-295 with snarkjs' argument order:
 //   prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>
 //   prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
 //   prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]

@@ -639,6 +639,138 @@ int g16_synth_vkey(g16_synth* s, uint8_t* out) {
     });
 }
 
+// The circuit as an .r1cs file and a powers-of-tau file for it under the generator's tau, alpha, beta: the inputs of
+// `zkey new` (g16_zkey_new).  The ceremony file has power = log2(domain) + 1 and the iden3 layout, but ONLY the ranges
+// `zkey new` reads for this circuit are populated (tauG1 monomial 0 .. 2n-2, first points of sections 4 and 5, betaG2,
+// Lagrange levels log2 n of sections 12-15 and log2 n + 1 of section 12); everything else is a hole in a sparse file.
+int g16_synth_write_setup_inputs(g16_synth* s, const char* r1cs_path, const char* ptau_path) {
+    return sguard([&]() {
+        if (!s || !r1cs_path || !ptau_path) return sfail("null argument");
+        Circuit& ci = s->circ;
+        Tables& T = tables();
+        // ---- .r1cs: header, constraints, wire-to-label map
+        {
+            std::vector<uint8_t> body;
+            body.reserve(size_t(ci.n_constraints) * 5 * 36);
+            Cons k;
+            auto put_lc = [&](const Term* t, int n) {
+                uint32_t cnt = (uint32_t)n;
+                body.insert(body.end(), (uint8_t*)&cnt, (uint8_t*)&cnt + 4);
+                for (int i = 0; i < n; i++) {
+                    body.insert(body.end(), (const uint8_t*)&t[i].wire, (const uint8_t*)&t[i].wire + 4);
+                    body.insert(body.end(), (const uint8_t*)t[i].coef.v, (const uint8_t*)t[i].coef.v + 32);
+                }
+            };
+            for (uint32_t c = 0; c < ci.n_constraints; c++) {
+                ci.constraint(c, k);
+                put_lc(k.A, k.nA);
+                put_lc(k.B, k.nB);
+                put_lc(k.C, k.nC);
+            }
+            std::vector<uint8_t> head(4 + 32 + 16 + 8 + 4);
+            uint8_t* p = head.data();
+            wr32(p, 32);
+            std::memcpy(p, HFr::mod().v, 32);
+            p += 32;
+            wr32(p, ci.n_vars);
+            wr32(p, 0);
+            wr32(p, ci.n_public);
+            wr32(p, ci.n_vars - 1 - ci.n_public);
+            uint64_t labels = ci.n_vars;
+            std::memcpy(p, &labels, 8);
+            p += 8;
+            wr32(p, ci.n_constraints);
+            std::vector<uint64_t> map(ci.n_vars);
+            for (uint32_t i = 0; i < ci.n_vars; i++) map[i] = i;
+            FILE* f = std::fopen(r1cs_path, "wb");
+            if (!f) return sfail(std::string("cannot write ") + r1cs_path);
+            auto sec = [&](uint32_t typ, const void* data, uint64_t size) {
+                std::fwrite(&typ, 4, 1, f);
+                std::fwrite(&size, 8, 1, f);
+                if (size) std::fwrite(data, 1, size, f);
+            };
+            uint32_t ver = 1, nsec = 3;
+            std::fwrite("r1cs", 1, 4, f);
+            std::fwrite(&ver, 4, 1, f);
+            std::fwrite(&nsec, 4, 1, f);
+            sec(1, head.data(), head.size());
+            sec(2, body.data(), body.size());
+            sec(3, map.data(), map.size() * 8);
+            if (std::fclose(f) != 0) return sfail(std::string("short write to ") + r1cs_path);
+        }
+        // ---- .ptau (sparse)
+        const int k = ci.log_n, power = k + 1;
+        const uint64_t n = ci.domain, P = uint64_t(1) << power;
+        struct S { uint32_t typ; uint64_t size, off; };
+        std::vector<S> secs = {{1, 4 + 32 + 8, 0}, {2, (2 * P - 1) * 64, 0}, {3, P * 128, 0}, {4, P * 64, 0}, {5, P * 64, 0},
+                               {6, 128, 0}, {7, 4, 0}, {12, (2 * P - 1 + 2 * P) * 64, 0}, {13, (2 * P - 1) * 128, 0},
+                               {14, (2 * P - 1) * 64, 0}, {15, (2 * P - 1) * 64, 0}};
+        uint64_t pos = 12;
+        for (S& x : secs) { x.off = pos + 12; pos += 12 + x.size; }
+        FILE* f = std::fopen(ptau_path, "wb");
+        if (!f) return sfail(std::string("cannot write ") + ptau_path);
+        auto at = [&](uint64_t off, const void* data, size_t len) {
+            if (fseeko(f, (off_t)off, SEEK_SET) != 0 || std::fwrite(data, 1, len, f) != len) throw std::runtime_error(std::string("cannot write ") + ptau_path);
+        };
+        auto off_of = [&](uint32_t typ) { for (S& x : secs) if (x.typ == typ) return x.off; return uint64_t(0); };
+        {
+            uint32_t ver = 1, nsec = (uint32_t)secs.size();
+            at(0, "ptau", 4);
+            at(4, &ver, 4);
+            at(8, &nsec, 4);
+            for (S& x : secs) { at(x.off - 12, &x.typ, 4); at(x.off - 8, &x.size, 8); }
+            uint8_t h[4 + 32 + 8];
+            uint8_t* p = h;
+            wr32(p, 32);
+            std::memcpy(p, HFq::mod().v, 32);
+            p += 32;
+            wr32(p, (uint32_t)power);
+            wr32(p, (uint32_t)power);
+            at(off_of(1), h, sizeof h);
+            uint32_t zero = 0;
+            at(off_of(7), &zero, 4);
+        }
+        std::vector<uint8_t> rec;
+        auto g1_points = [&](const std::vector<fr>& sc, uint64_t off) {
+            rec.resize(sc.size() * 64);
+            emit_points<G1>(T.g1, sc, rec.data());
+            at(off, rec.data(), rec.size());
+        };
+        auto scaled = [&](const std::vector<fr>& v, const fr& m) {
+            std::vector<fr> o(v.size());
+            for (size_t i = 0; i < v.size(); i++) o[i] = HFr::mul(v[i], m);
+            return o;
+        };
+        {   // monomial tauG1: tau^0 .. tau^(2n-2)
+            std::vector<fr> tp(2 * n - 1);
+            tp[0] = HFr::one();
+            for (size_t i = 1; i < tp.size(); i++) tp[i] = HFr::mul(tp[i - 1], s->tau);
+            g1_points(tp, off_of(2));
+        }
+        g1_points({s->alpha}, off_of(4));
+        g1_points({s->beta}, off_of(5));
+        {
+            uint8_t b2[128];
+            emit_points<G2>(T.g2, {s->beta}, b2);
+            at(off_of(6), b2, 128);
+        }
+        {   // Lagrange level k of sections 12-15, level k+1 of section 12
+            std::vector<fr> L = lagrange_at(s->tau, k);
+            g1_points(L, off_of(12) + (n - 1) * 64);
+            g1_points(scaled(L, s->alpha), off_of(14) + (n - 1) * 64);
+            g1_points(scaled(L, s->beta), off_of(15) + (n - 1) * 64);
+            rec.resize(L.size() * 128);
+            emit_points<G2>(T.g2, L, rec.data());
+            at(off_of(13) + (n - 1) * 128, rec.data(), rec.size());
+            g1_points(lagrange_at(s->tau, k + 1), off_of(12) + (2 * n - 1) * 64);
+        }
+        // the file's full length (the tail may be a hole)
+        if (fseeko(f, (off_t)(pos - 1), SEEK_SET) != 0 || std::fwrite("", 1, 1, f) != 1) { std::fclose(f); return sfail("cannot size the ptau file"); }
+        if (std::fclose(f) != 0) return sfail(std::string("short write to ") + ptau_path);
+        return 0;
+    });
+}
+
 int g16_synth_fixed_base(int is_g2, const uint8_t* scalars, size_t n, uint8_t* out) {
     return sguard([&]() {
         if (!scalars || !out) return sfail("null argument");

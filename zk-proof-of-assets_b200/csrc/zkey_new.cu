@@ -1,6 +1,6 @@
 // `snarkjs zkey new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>` on the GPU -- SURVEY.md 8(f) rank 2, first step.
 //
-// Replaces what scripts/g16_setup.sh:240-252 of the reference runs through snarkjs 0.7.2 (`groth16 setup`, src/zkey_new.js;
+// Replaces what scripts/g16_setup.sh:239-254 of the reference runs through snarkjs 0.7.2 (`groth16 setup`, src/zkey_new.js;
 // the step before the contributions of csrc/setup.cpp).  From a circuit and a ceremony file prepared for phase 2 it
 // builds the whole proving key: header, IC, coefficients, A, B1, B2, C, H and the contributions section with the
 // circuit hash.  Everything heavy is a SPARSE LINEAR COMBINATION OF POINTS: with L_c the ceremony's Lagrange-form points
