@@ -17,9 +17,13 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
+#include <thread>
 #include <vector>
 
 #include "../../include/g16_b200.h"
@@ -50,14 +54,16 @@ __device__ __forceinline__ bool gt256(const uint32_t* a, const uint32_t* b) {
 // partial[chunk] = sum over the chunk's terms of coef * table[src]
 template <class C>
 __global__ void __launch_bounds__(128)
-lincomb_chunk_kernel(const uint64_t* __restrict__ chunk_begin, const uint32_t* __restrict__ chunk_len, size_t n_chunks,
+lincomb_chunk_kernel(const uint64_t* __restrict__ order, const uint64_t* __restrict__ chunk_begin,
+                     const uint32_t* __restrict__ chunk_len, size_t n_chunks,
                      const uint32_t* __restrict__ src, const RawScalar* __restrict__ coef,
                      const typename C::aff* __restrict__ table, typename C::pt* __restrict__ partial) {
     typedef typename C::field F;
     typedef typename C::aff aff;
     typedef typename C::pt pt;
-    size_t t = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
-    if (t >= n_chunks) return;
+    size_t th = blockIdx.x * size_t(blockDim.x) + threadIdx.x;
+    if (th >= n_chunks) return;
+    const uint64_t t = order[th];   // cheap chunks first, full-width terms together at the end
     pt acc = C::identity();
     uint64_t at = chunk_begin[t];
     for (uint32_t e = 0; e < chunk_len[t]; e++, at++) {
@@ -225,30 +231,63 @@ struct Csr {     // the same, grouped by row and cut into chunks of at most LC_C
     std::vector<RawScalar> coef;
     std::vector<uint64_t> chunk_begin, row_chunk;
     std::vector<uint32_t> chunk_len;
+    std::vector<uint64_t> order;   // chunks in the order threads take them: the cheap ones, then the full-width terms
 };
+
+// a term whose coefficient (or its negative) needs more than 40 doublings: it gets a chunk, i.e. a thread, of its own, and
+// those chunks run together at the end of the launch -- a warp is then all +-1 / small constants or all long scalars,
+// instead of 31 lanes waiting for the one that drew a 254-bit coefficient
+bool heavy_term(const RawScalar& k) {
+    static const U256 r = HFr::mod();
+    U256 v;
+    std::memcpy(v.v, k.v, 32);
+    U256 neg = HFr::raw_sub(r, v);
+    const U256& m = u256_cmp(v, neg) <= 0 ? v : neg;
+    return m.v[3] || m.v[2] || m.v[1] || (m.v[0] >> 40);
+}
 
 Csr group_rows(const Terms& t, size_t n_rows) {
     Csr c;
-    std::vector<uint64_t> start(n_rows + 1, 0);
-    for (uint32_t r : t.row) start[r + 1]++;
+    const size_t nt = t.row.size();
+    std::vector<uint8_t> heavy(nt);
+    for (size_t i = 0; i < nt; i++) heavy[i] = heavy_term(t.coef[i]) ? 1 : 0;
+    // per row: light terms first, then heavy ones
+    std::vector<uint64_t> start(n_rows + 1, 0), n_heavy(n_rows, 0);
+    for (size_t i = 0; i < nt; i++) {
+        start[t.row[i] + 1]++;
+        n_heavy[t.row[i]] += heavy[i];
+    }
     for (size_t r = 0; r < n_rows; r++) start[r + 1] += start[r];
-    c.src.resize(t.row.size());
-    c.coef.resize(t.row.size());
-    std::vector<uint64_t> cur(start.begin(), start.end() - 1);
-    for (size_t i = 0; i < t.row.size(); i++) {
-        uint64_t at = cur[t.row[i]]++;
+    c.src.resize(nt);
+    c.coef.resize(nt);
+    std::vector<uint64_t> cur_l(n_rows), cur_h(n_rows);
+    for (size_t r = 0; r < n_rows; r++) {
+        cur_l[r] = start[r];
+        cur_h[r] = start[r + 1] - n_heavy[r];
+    }
+    for (size_t i = 0; i < nt; i++) {
+        uint64_t at = heavy[i] ? cur_h[t.row[i]]++ : cur_l[t.row[i]]++;
         c.src[at] = t.src[i];
         c.coef[at] = t.coef[i];
     }
     c.row_chunk.resize(n_rows + 1);
+    std::vector<uint64_t> late;
     for (size_t r = 0; r < n_rows; r++) {
         c.row_chunk[r] = c.chunk_begin.size();
-        for (uint64_t at = start[r]; at < start[r + 1]; at += LC_CHUNK) {
+        const uint64_t light_end = start[r + 1] - n_heavy[r];
+        for (uint64_t at = start[r]; at < light_end; at += LC_CHUNK) {
+            c.order.push_back(c.chunk_begin.size());
             c.chunk_begin.push_back(at);
-            c.chunk_len.push_back(uint32_t(std::min<uint64_t>(LC_CHUNK, start[r + 1] - at)));
+            c.chunk_len.push_back(uint32_t(std::min<uint64_t>(LC_CHUNK, light_end - at)));
+        }
+        for (uint64_t at = light_end; at < start[r + 1]; at++) {
+            late.push_back(c.chunk_begin.size());
+            c.chunk_begin.push_back(at);
+            c.chunk_len.push_back(1);
         }
     }
     c.row_chunk[n_rows] = c.chunk_begin.size();
+    c.order.insert(c.order.end(), late.begin(), late.end());
     return c;
 }
 
@@ -265,7 +304,8 @@ std::vector<uint8_t> run_lincomb(const Csr& c, const void* d_table, size_t n_row
     typedef typename C::pt pt;
     std::vector<uint8_t> out(n_rows * sizeof(aff));
     if (!n_rows) return out;
-    DevBuf d_src, d_coef, d_cb, d_cl, d_rc, d_part, d_out;
+    DevBuf d_src, d_coef, d_cb, d_cl, d_rc, d_part, d_out, d_order;
+    upload(d_order, c.order);
     upload(d_src, c.src);
     upload(d_coef, c.coef);
     upload(d_cb, c.chunk_begin);
@@ -275,7 +315,7 @@ std::vector<uint8_t> run_lincomb(const Csr& c, const void* d_table, size_t n_row
     d_part.alloc((nch ? nch : 1) * sizeof(pt));
     d_out.alloc(n_rows * sizeof(aff));
     if (nch) {
-        lincomb_chunk_kernel<C><<<(unsigned)((nch + 127) / 128), 128>>>(d_cb.as<uint64_t>(), d_cl.as<uint32_t>(), nch, d_src.as<uint32_t>(),
+        lincomb_chunk_kernel<C><<<(unsigned)((nch + 127) / 128), 128>>>(d_order.as<uint64_t>(), d_cb.as<uint64_t>(), d_cl.as<uint32_t>(), nch, d_src.as<uint32_t>(),
                                                                         d_coef.as<RawScalar>(), static_cast<const aff*>(d_table), d_part.as<pt>());
         G16_CUDA(cudaGetLastError());
     }
@@ -298,26 +338,38 @@ bool all_zero(const uint8_t* p, size_t n) {
     return true;
 }
 
-// ffjavascript toRprUncompressed: G1 = x | y, G2 = x.c1 | x.c0 | y.c1 | y.c0, big-endian standard form; infinity = 0x40, zeros
+// ffjavascript toRprUncompressed: G1 = x | y, G2 = x.c1 | x.c0 | y.c1 | y.c0, big-endian standard form; infinity = 0x40, zeros.
+// The conversion (a Montgomery reduction per coordinate) runs on the host's cores; the hash itself is sequential.
 void hash_points(g16setup::Blake2b& h, const uint8_t* recs, size_t count, bool g2, bool with_count = true) {
     if (with_count) {
         uint8_t be[4] = {uint8_t(count >> 24), uint8_t(count >> 16), uint8_t(count >> 8), uint8_t(count)};
         h.update(be, 4);
     }
     const size_t rec = g2 ? 128 : 64;
-    uint8_t u[128];
-    for (size_t i = 0; i < count; i++) {
-        const uint8_t* p = recs + i * rec;
-        if (all_zero(p, rec)) {
-            std::memset(u, 0, rec);
-            u[0] = 0x40;
-        } else if (g2) {
-            be32(u, p + 32); be32(u + 32, p); be32(u + 64, p + 96); be32(u + 96, p + 64);
-        } else {
-            be32(u, p); be32(u + 32, p + 32);
+    std::vector<uint8_t> buf(count * rec);
+    auto convert = [&](size_t lo, size_t hi) {
+        for (size_t i = lo; i < hi; i++) {
+            const uint8_t* p = recs + i * rec;
+            uint8_t* u = &buf[i * rec];
+            if (all_zero(p, rec)) {
+                std::memset(u, 0, rec);
+                u[0] = 0x40;
+            } else if (g2) {
+                be32(u, p + 32); be32(u + 32, p); be32(u + 64, p + 96); be32(u + 96, p + 64);
+            } else {
+                be32(u, p); be32(u + 32, p + 32);
+            }
         }
-        h.update(u, rec);
+    };
+    unsigned nth = std::thread::hardware_concurrency();
+    if (nth > 16) nth = 16;
+    if (nth < 2 || count < 4096) convert(0, count);
+    else {
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nth; k++) th.emplace_back(convert, count * k / nth, count * (k + 1) / nth);
+        for (auto& x : th) x.join();
     }
+    h.update(buf.data(), buf.size());
 }
 
 void put_section(std::vector<uint8_t>& file, uint32_t typ, const void* data, uint64_t size) {
@@ -361,6 +413,13 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
     try {
         if (!r1cs_path || !ptau_path || !zkey_out) return fail(G16_ERR_GENERIC, "null argument");
         use_device(opts);
+        const bool verbose = std::getenv("G16_VERBOSE") != nullptr;
+        auto t_last = std::chrono::steady_clock::now();
+        auto phase = [&](const char* what) {   // G16_VERBOSE=1: where the time goes, on stderr
+            auto now = std::chrono::steady_clock::now();
+            if (verbose) std::fprintf(stderr, "[zkey new] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(now - t_last).count());
+            t_last = now;
+        };
         // ---- the circuit
         FileRO fr(r1cs_path);
         auto rs = scan_sections(fr, "r1cs");
@@ -409,6 +468,7 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             tab1.insert(tab1.end(), b.begin(), b.end());
         }
         std::vector<uint8_t> tab2 = read_points(fp, ps[13], n - 1, n, 128, "13");
+        phase("ceremony points read");
         // ---- the terms
         const Sec& r2 = need_sec(rs, 2, "r1cs");
         std::vector<uint8_t> body(r2.size);
@@ -466,6 +526,7 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             coef_record(0, n_cons + s, s, U256{{1, 0, 0, 0}});
         }
         std::memcpy(sec4.data(), &n_coefs, 4);
+        phase("circuit parsed");
         // ---- the sections, on the GPU
         {
             U256 half = rmod;
@@ -481,18 +542,25 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         {
             Csr c = group_rows(tA, n_vars);
             tA = Terms();
+            phase("A grouped");
             secA = run_lincomb<G1>(c, d_tab1.p, n_vars);
+            phase("A on the GPU");
         }
         {
             Csr c = group_rows(tB, n_vars);
             tB = Terms();
+            phase("B grouped");
             secB1 = run_lincomb<G1>(c, d_tab1.p, n_vars);
+            phase("B1 on the GPU");
             secB2 = run_lincomb<G2>(c, d_tab2.p, n_vars);
+            phase("B2 on the GPU");
         }
         {
             Csr c = group_rows(tM, n_vars);
             tM = Terms();
+            phase("IC/C grouped");
             secM = run_lincomb<G1>(c, d_tab1.p, n_vars);
+            phase("IC/C on the GPU");
         }
         d_tab1.free();
         d_tab2.free();
@@ -514,6 +582,7 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             G16_LAUNCHED(1);
             G16_CUDA(cudaMemcpy(hdiff.data(), d_out.p, hdiff.size(), cudaMemcpyDeviceToHost));
         }
+        phase("H copied, tau differences");
         // ---- header, circuit hash, file
         uint8_t alpha1[64], beta1[64], beta2[128], g1[64], g2[128];
         fp.read(need_sec(ps, 4, "ptau").off, alpha1, 64);
@@ -536,6 +605,7 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         hash_points(h, secB1.data(), n_vars, false);
         hash_points(h, secB2.data(), n_vars, true);
         std::vector<uint8_t> cs = h.digest();
+        phase("circuit hash");
         if (cs_hash_out) std::memcpy(cs_hash_out, cs.data(), 64);
         std::vector<uint8_t> file;
         file.reserve(64 + sec4.size() + secA.size() * 3 + secB2.size() + secH.size() + 1024);
@@ -574,6 +644,7 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             ::close(fd);
         }
         if (std::rename(tmp.c_str(), zkey_out) != 0) { ::unlink(tmp.c_str()); throw std::runtime_error(std::string("cannot rename onto ") + zkey_out); }
+        phase("file written");
         return (int)G16_OK;
     } catch (const std::exception& e) {
         std::string m = e.what();
