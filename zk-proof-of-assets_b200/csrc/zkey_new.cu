@@ -211,12 +211,19 @@ const Sec& need_sec(const std::map<uint32_t, Sec>& m, uint32_t typ, const std::s
     return it->second;
 }
 
-std::vector<uint8_t> read_points(const FileRO& f, const Sec& s, uint64_t first, uint64_t count, size_t rec, const char* what) {
+struct RawBuf {   // bytes without the zero fill of a std::vector (these buffers are gigabytes and written in full)
+    std::unique_ptr<uint8_t[]> p;
+    size_t n = 0;
+    explicit RawBuf(size_t bytes) : p(new uint8_t[bytes ? bytes : 1]), n(bytes) {}
+    uint8_t* data() { return p.get(); }
+    size_t size() const { return n; }
+    void free() { p.reset(); n = 0; }
+};
+
+void read_points_into(const FileRO& f, const Sec& s, uint64_t first, uint64_t count, size_t rec, const char* what, uint8_t* dst) {
     if ((first + count) * rec > s.size)
         throw std::runtime_error(std::string("ptau: section ") + what + " is too short for this circuit (powers of tau too small)");
-    std::vector<uint8_t> out(count * rec);
-    f.read(s.off + first * rec, out.data(), out.size());
-    return out;
+    f.read(s.off + first * rec, dst, count * rec);
 }
 
 // ---- host side: the term lists ---------------------------------------------------------------------------------------
@@ -372,14 +379,6 @@ void hash_points(g16setup::Blake2b& h, const uint8_t* recs, size_t count, bool g
     h.update(buf.data(), buf.size());
 }
 
-void put_section(std::vector<uint8_t>& file, uint32_t typ, const void* data, uint64_t size) {
-    size_t at = file.size();
-    file.resize(at + 12 + size);
-    std::memcpy(&file[at], &typ, 4);
-    std::memcpy(&file[at + 4], &size, 8);
-    if (size) std::memcpy(&file[at + 12], data, size);
-}
-
 void use_device(const g16_opts* o) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
@@ -461,13 +460,11 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         for (uint32_t t : {12u, 13u, 14u, 15u})
             if (!ps.count(t)) return fail(G16_ERR_FORMAT, "ptau: not prepared for phase 2 (section " + std::to_string(t) + " missing)");
         // Lagrange points of the circuit's domain; one G1 table [tauG1 | alphaTauG1 | betaTauG1] for the mixed section
-        std::vector<uint8_t> tab1 = read_points(fp, ps[12], n - 1, n, 64, "12");
-        {
-            std::vector<uint8_t> a = read_points(fp, ps[14], n - 1, n, 64, "14"), b = read_points(fp, ps[15], n - 1, n, 64, "15");
-            tab1.insert(tab1.end(), a.begin(), a.end());
-            tab1.insert(tab1.end(), b.begin(), b.end());
-        }
-        std::vector<uint8_t> tab2 = read_points(fp, ps[13], n - 1, n, 128, "13");
+        RawBuf tab1(3 * n * 64), tab2(n * 128);
+        read_points_into(fp, ps[12], n - 1, n, 64, "12", tab1.data());
+        read_points_into(fp, ps[14], n - 1, n, 64, "14", tab1.data() + n * 64);
+        read_points_into(fp, ps[15], n - 1, n, 64, "15", tab1.data() + 2 * n * 64);
+        read_points_into(fp, ps[13], n - 1, n, 128, "13", tab2.data());
         phase("ceremony points read");
         // ---- the terms
         const Sec& r2 = need_sec(rs, 2, "r1cs");
@@ -478,13 +475,19 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         uint32_t n_coefs = 0;
         const U256 rmod = HFr::mod();
         size_t pos = 0;
+        const U256 r3 = HFr::to_mont(HFr::to_mont(HFr::to_mont(U256{{1, 0, 0, 0}})));   // R^3 mod r
+        {   // an upper bound of the term count, so that the lists grow without reallocation
+            size_t cap = body.size() / 36 + size_t(n_pub) + 1;
+            for (Terms* t : {&tA, &tB, &tM}) { t->row.reserve(cap); t->src.reserve(cap); t->coef.reserve(cap); }
+            sec4.reserve(4 + cap * 44);
+        }
         auto coef_record = [&](uint32_t m, uint32_t c, uint32_t s, const U256& v) {
             size_t at = sec4.size();
             sec4.resize(at + 44);
             std::memcpy(&sec4[at], &m, 4);
             std::memcpy(&sec4[at + 4], &c, 4);
             std::memcpy(&sec4[at + 8], &s, 4);
-            u256_to_bytes(HFr::to_mont(HFr::to_mont(v)), &sec4[at + 12]);   // x R^2: snarkjs's convention for section 4
+            u256_to_bytes(HFr::mul(v, r3), &sec4[at + 12]);   // x R^2 (one Montgomery product by R^3): snarkjs's convention for section 4
             n_coefs++;
         };
         for (uint32_t c = 0; c < n_cons; c++) {
@@ -536,8 +539,12 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             G16_CUDA(cudaMemcpyToSymbol(ZN_HALF, half.v, 32));
         }
         DevBuf d_tab1, d_tab2;
-        upload(d_tab1, tab1);
-        upload(d_tab2, tab2);
+        d_tab1.alloc(tab1.size());
+        d_tab2.alloc(tab2.size());
+        G16_CUDA(cudaMemcpy(d_tab1.p, tab1.data(), tab1.size(), cudaMemcpyHostToDevice));
+        G16_CUDA(cudaMemcpy(d_tab2.p, tab2.data(), tab2.size(), cudaMemcpyHostToDevice));
+        tab1.free();
+        tab2.free();
         std::vector<uint8_t> secA, secB1, secB2, secM;
         {
             Csr c = group_rows(tA, n_vars);
@@ -565,17 +572,20 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         d_tab1.free();
         d_tab2.free();
         // H: the odd Lagrange points of the domain of twice the size
-        std::vector<uint8_t> secH(n * 64);
+        RawBuf secH(n * 64);
         {
-            std::vector<uint8_t> top = read_points(fp, ps[12], 2 * n - 1, 2 * n, 64, "12");
-            for (uint64_t i = 0; i < n; i++) std::memcpy(&secH[i * 64], &top[(2 * i + 1) * 64], 64);
+            RawBuf top(2 * n * 64);
+            read_points_into(fp, ps[12], 2 * n - 1, 2 * n, 64, "12", top.data());
+            for (uint64_t i = 0; i < n; i++) std::memcpy(secH.data() + i * 64, top.data() + (2 * i + 1) * 64, 64);
         }
         // the points the circuit hash covers for H: tau^(i+n) - tau^i
         std::vector<uint8_t> hdiff((n - 1) * 64);
         if (n > 1) {
-            std::vector<uint8_t> mono = read_points(fp, need_sec(ps, 2, "ptau"), 0, 2 * n - 1, 64, "2");
+            RawBuf mono((2 * n - 1) * 64);
+            read_points_into(fp, need_sec(ps, 2, "ptau"), 0, 2 * n - 1, 64, "2", mono.data());
             DevBuf d_mono, d_out;
-            upload(d_mono, mono);
+            d_mono.alloc(mono.size());
+            G16_CUDA(cudaMemcpy(d_mono.p, mono.data(), mono.size(), cudaMemcpyHostToDevice));
             d_out.alloc(hdiff.size());
             tau_diff_kernel<<<(unsigned)((n - 1 + 127) / 128), 128>>>(d_mono.as<g1_aff>(), (uint32_t)n, (uint32_t)(n - 1), d_out.as<g1_aff>());
             G16_CUDA(cudaGetLastError());
@@ -607,41 +617,49 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         std::vector<uint8_t> cs = h.digest();
         phase("circuit hash");
         if (cs_hash_out) std::memcpy(cs_hash_out, cs.data(), 64);
-        std::vector<uint8_t> file;
-        file.reserve(64 + sec4.size() + secA.size() * 3 + secB2.size() + secH.size() + 1024);
-        file.insert(file.end(), {'z', 'k', 'e', 'y', 1, 0, 0, 0, 10, 0, 0, 0});
-        uint32_t proto = 1;
-        put_section(file, 1, &proto, 4);
         std::vector<uint8_t> hd;
         auto push = [&](const void* p, size_t len) { hd.insert(hd.end(), (const uint8_t*)p, (const uint8_t*)p + len); };
-        uint32_t v32 = 32, dom = (uint32_t)n;
+        uint32_t v32 = 32, dom = (uint32_t)n, proto = 1;
         uint8_t qb[32], rb[32];
         u256_to_bytes(HFq::mod(), qb);
         u256_to_bytes(rmod, rb);
         push(&v32, 4); push(qb, 32); push(&v32, 4); push(rb, 32);
         push(&n_vars, 4); push(&n_pub, 4); push(&dom, 4);
         push(alpha1, 64); push(beta1, 64); push(beta2, 128); push(g2, 128); push(g1, 64); push(g2, 128);
-        put_section(file, 2, hd.data(), hd.size());
-        put_section(file, 3, secM.data(), n_ic * 64);
-        put_section(file, 4, sec4.data(), sec4.size());
-        put_section(file, 5, secA.data(), secA.size());
-        put_section(file, 6, secB1.data(), secB1.size());
-        put_section(file, 7, secB2.data(), secB2.size());
-        put_section(file, 8, secM.data() + n_ic * 64, (n_vars - n_ic) * 64);
-        put_section(file, 9, secH.data(), secH.size());
         cs.resize(68, 0);   // u32 0 contributions
-        put_section(file, 10, cs.data(), 68);
         std::string tmp = std::string(zkey_out) + ".tmp." + std::to_string((long)getpid());
         {
             int fd = ::open(tmp.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
             if (fd < 0) throw std::runtime_error("cannot write " + tmp);
-            size_t done = 0;
-            while (done < file.size()) {
-                ssize_t w = ::write(fd, file.data() + done, file.size() - done);
-                if (w <= 0) { ::close(fd); ::unlink(tmp.c_str()); throw std::runtime_error("short write to " + tmp); }
-                done += (size_t)w;
-            }
-            ::close(fd);
+            auto put = [&](const void* data, uint64_t len) {
+                const uint8_t* p = static_cast<const uint8_t*>(data);
+                while (len) {
+                    ssize_t w = ::write(fd, p, len > (uint64_t(1) << 30) ? size_t(1) << 30 : size_t(len));
+                    if (w <= 0) { ::close(fd); ::unlink(tmp.c_str()); throw std::runtime_error("short write to " + tmp); }
+                    p += w;
+                    len -= (uint64_t)w;
+                }
+            };
+            auto section = [&](uint32_t typ, const void* data, uint64_t size) {
+                uint8_t h12[12];
+                std::memcpy(h12, &typ, 4);
+                std::memcpy(h12 + 4, &size, 8);
+                put(h12, 12);
+                put(data, size);
+            };
+            const uint8_t magic[12] = {'z', 'k', 'e', 'y', 1, 0, 0, 0, 10, 0, 0, 0};
+            put(magic, 12);
+            section(1, &proto, 4);
+            section(2, hd.data(), hd.size());
+            section(3, secM.data(), n_ic * 64);
+            section(4, sec4.data(), sec4.size());
+            section(5, secA.data(), secA.size());
+            section(6, secB1.data(), secB1.size());
+            section(7, secB2.data(), secB2.size());
+            section(8, secM.data() + n_ic * 64, (n_vars - n_ic) * 64);
+            section(9, secH.data(), secH.size());
+            section(10, cs.data(), 68);
+            if (::close(fd) != 0) { ::unlink(tmp.c_str()); throw std::runtime_error("short write to " + tmp); }
         }
         if (std::rename(tmp.c_str(), zkey_out) != 0) { ::unlink(tmp.c_str()); throw std::runtime_error(std::string("cannot rename onto ") + zkey_out); }
         phase("file written");
