@@ -38,11 +38,13 @@ def main():
     args = ap.parse_args()
     sock = "/tmp/g16_bench_cli.%d.sock" % os.getpid()
     for name in args.workloads.split(","):
-        bench.fixture(name)
+        bench.fixture(name, load=False)
         zp, wp = os.path.join(bench.CACHE_DIR, name + ".zkey"), os.path.join(bench.CACHE_DIR, name + ".wtns")
         out = ["/tmp/g16_cli_proof.json", "/tmp/g16_cli_public.json"]
         env = dict(os.environ)
         env.pop("G16_SERVICE", None)
+        env.pop("CUDA_DEVICE_MAX_CONNECTIONS", None)     # importing bench set it for THIS process; the command line decides for itself
+        env.pop("G16_CONNECTIONS_DEFAULTED", None)
         cold = [timed([EXE, zp, wp] + out, env)[0] for _ in range(args.runs)]
         ref_proof = open(out[0]).read()
         srv = subprocess.Popen([EXE, "--serve", "--socket", sock, "--devices", args.devices], stderr=subprocess.DEVNULL)

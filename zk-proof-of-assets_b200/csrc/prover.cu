@@ -33,8 +33,14 @@ namespace g16 {
 // CUDA_DEVICE_MAX_CONNECTIONS hardware queues (default 8); streams that share a queue pick up false dependencies on each
 // other (measured: the H preparation waited 5 ms behind another stream's accumulations, 14.6 -> 13.9 ms per proof at
 // 2^21 once every stream has its own queue).  The variable is read when the CUDA context is created, so it is set when
-// the library is loaded, without overriding the user's choice.
-static const int g_max_connections_set = [] { return ::setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }();
+// the library is loaded, without overriding the user's choice.  The extra queues cost context-creation time (measured:
+// 0.8 -> 1.4 s), which a process that makes ONE proof never earns back: G16_CONNECTIONS_DEFAULTED tells such a caller (the
+// one-shot command line, csrc/prover_main.cpp) that the value is this library's default and may be lowered again.
+static const int g_max_connections_set = [] {
+    if (std::getenv("CUDA_DEVICE_MAX_CONNECTIONS")) return 0;
+    ::setenv("G16_CONNECTIONS_DEFAULTED", "1", 1);
+    return ::setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 1);
+}();
 
 thread_local std::string g_last_error;
 
