@@ -18,6 +18,9 @@
 #include <unistd.h>
 
 #include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -379,6 +382,61 @@ void hash_points(g16setup::Blake2b& h, const uint8_t* recs, size_t count, bool g
     h.update(buf.data(), buf.size());
 }
 
+// The circuit hash is sequential over the sections in a fixed order, and each section is ready long before the next one:
+// a worker thread hashes the jobs in the order they are pushed while the GPU computes the following section.
+class HashWorker {
+public:
+    HashWorker() : h_(64), th_([this] { run(); }) {}
+    ~HashWorker() { stop(); }
+    void push(const uint8_t* recs, size_t count, bool g2, bool with_count = true) {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            q_.push_back(Job{recs, count, g2, with_count});
+        }
+        cv_.notify_one();
+    }
+    std::vector<uint8_t> finish() {   // waits for every pushed job
+        stop();
+        if (err_) std::rethrow_exception(err_);
+        return h_.digest();
+    }
+
+private:
+    struct Job { const uint8_t* recs; size_t count; bool g2, with_count; };
+    void stop() {
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            done_ = true;
+        }
+        cv_.notify_one();
+        if (th_.joinable()) th_.join();
+    }
+    void run() {
+        try {
+            for (;;) {
+                Job j;
+                {
+                    std::unique_lock<std::mutex> lk(mu_);
+                    cv_.wait(lk, [this] { return done_ || !q_.empty(); });
+                    if (q_.empty()) return;
+                    j = q_.front();
+                    q_.pop_front();
+                }
+                hash_points(h_, j.recs, j.count, j.g2, j.with_count);
+            }
+        } catch (...) {
+            err_ = std::current_exception();
+        }
+    }
+    g16setup::Blake2b h_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<Job> q_;
+    bool done_ = false;
+    std::exception_ptr err_;
+    std::thread th_;   // last member: starts after everything above exists
+};
+
 void use_device(const g16_opts* o) {
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
@@ -545,23 +603,26 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
         G16_CUDA(cudaMemcpy(d_tab2.p, tab2.data(), tab2.size(), cudaMemcpyHostToDevice));
         tab1.free();
         tab2.free();
+        // Order of work = order of the circuit hash (header points | IC | tau differences | C | A | B1 | B2): the hash worker
+        // takes each section as soon as it is back from the GPU.  The buffers live until the end of this function; the
+        // worker is declared after them, so it is joined before they go.
         std::vector<uint8_t> secA, secB1, secB2, secM;
-        {
-            Csr c = group_rows(tA, n_vars);
-            tA = Terms();
-            phase("A grouped");
-            secA = run_lincomb<G1>(c, d_tab1.p, n_vars);
-            phase("A on the GPU");
-        }
-        {
-            Csr c = group_rows(tB, n_vars);
-            tB = Terms();
-            phase("B grouped");
-            secB1 = run_lincomb<G1>(c, d_tab1.p, n_vars);
-            phase("B1 on the GPU");
-            secB2 = run_lincomb<G2>(c, d_tab2.p, n_vars);
-            phase("B2 on the GPU");
-        }
+        uint8_t alpha1[64], beta1[64], beta2[128], g1[64], g2[128];
+        fp.read(need_sec(ps, 4, "ptau").off, alpha1, 64);
+        fp.read(need_sec(ps, 5, "ptau").off, beta1, 64);
+        fp.read(need_sec(ps, 6, "ptau").off, beta2, 128);
+        g1_generator(g1);
+        g2_generator(g2);
+        const size_t n_ic = size_t(n_pub) + 1;
+        std::vector<uint8_t> hdiff((n - 1) * 64);
+        RawBuf secH(n * 64);
+        HashWorker hasher;
+        hasher.push(alpha1, 1, false, false);
+        hasher.push(beta1, 1, false, false);
+        hasher.push(beta2, 1, true, false);
+        hasher.push(g2, 1, true, false);
+        hasher.push(g1, 1, false, false);
+        hasher.push(g2, 1, true, false);
         {
             Csr c = group_rows(tM, n_vars);
             tM = Terms();
@@ -569,17 +630,8 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             secM = run_lincomb<G1>(c, d_tab1.p, n_vars);
             phase("IC/C on the GPU");
         }
-        d_tab1.free();
-        d_tab2.free();
-        // H: the odd Lagrange points of the domain of twice the size
-        RawBuf secH(n * 64);
-        {
-            RawBuf top(2 * n * 64);
-            read_points_into(fp, ps[12], 2 * n - 1, 2 * n, 64, "12", top.data());
-            for (uint64_t i = 0; i < n; i++) std::memcpy(secH.data() + i * 64, top.data() + (2 * i + 1) * 64, 64);
-        }
+        hasher.push(secM.data(), n_ic, false);
         // the points the circuit hash covers for H: tau^(i+n) - tau^i
-        std::vector<uint8_t> hdiff((n - 1) * 64);
         if (n > 1) {
             RawBuf mono((2 * n - 1) * 64);
             read_points_into(fp, need_sec(ps, 2, "ptau"), 0, 2 * n - 1, 64, "2", mono.data());
@@ -592,29 +644,39 @@ extern "C" int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const 
             G16_LAUNCHED(1);
             G16_CUDA(cudaMemcpy(hdiff.data(), d_out.p, hdiff.size(), cudaMemcpyDeviceToHost));
         }
-        phase("H copied, tau differences");
-        // ---- header, circuit hash, file
-        uint8_t alpha1[64], beta1[64], beta2[128], g1[64], g2[128];
-        fp.read(need_sec(ps, 4, "ptau").off, alpha1, 64);
-        fp.read(need_sec(ps, 5, "ptau").off, beta1, 64);
-        fp.read(need_sec(ps, 6, "ptau").off, beta2, 128);
-        g1_generator(g1);
-        g2_generator(g2);
-        const size_t n_ic = size_t(n_pub) + 1;
-        g16setup::Blake2b h(64);
-        hash_points(h, alpha1, 1, false, false);
-        hash_points(h, beta1, 1, false, false);
-        hash_points(h, beta2, 1, true, false);
-        hash_points(h, g2, 1, true, false);
-        hash_points(h, g1, 1, false, false);
-        hash_points(h, g2, 1, true, false);
-        hash_points(h, secM.data(), n_ic, false);
-        hash_points(h, hdiff.data(), n - 1, false);
-        hash_points(h, secM.data() + n_ic * 64, n_vars - n_ic, false);
-        hash_points(h, secA.data(), n_vars, false);
-        hash_points(h, secB1.data(), n_vars, false);
-        hash_points(h, secB2.data(), n_vars, true);
-        std::vector<uint8_t> cs = h.digest();
+        hasher.push(hdiff.data(), n - 1, false);
+        hasher.push(secM.data() + n_ic * 64, n_vars - n_ic, false);
+        phase("tau differences");
+        {
+            Csr c = group_rows(tA, n_vars);
+            tA = Terms();
+            phase("A grouped");
+            secA = run_lincomb<G1>(c, d_tab1.p, n_vars);
+            phase("A on the GPU");
+        }
+        hasher.push(secA.data(), n_vars, false);
+        {
+            Csr c = group_rows(tB, n_vars);
+            tB = Terms();
+            phase("B grouped");
+            secB1 = run_lincomb<G1>(c, d_tab1.p, n_vars);
+            phase("B1 on the GPU");
+            hasher.push(secB1.data(), n_vars, false);
+            secB2 = run_lincomb<G2>(c, d_tab2.p, n_vars);
+            phase("B2 on the GPU");
+        }
+        hasher.push(secB2.data(), n_vars, true);
+        d_tab1.free();
+        d_tab2.free();
+        // H: the odd Lagrange points of the domain of twice the size
+        {
+            RawBuf top(2 * n * 64);
+            read_points_into(fp, ps[12], 2 * n - 1, 2 * n, 64, "12", top.data());
+            for (uint64_t i = 0; i < n; i++) std::memcpy(secH.data() + i * 64, top.data() + (2 * i + 1) * 64, 64);
+        }
+        phase("H copied");
+        // ---- circuit hash (what is left of it), header, file
+        std::vector<uint8_t> cs = hasher.finish();
         phase("circuit hash");
         if (cs_hash_out) std::memcpy(cs_hash_out, cs.data(), 64);
         std::vector<uint8_t> hd;
