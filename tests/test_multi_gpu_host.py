@@ -32,6 +32,18 @@ def test_transform_owners_cover_the_three_polynomials():
         assert sum(masks) == 7 and all(m & k == 0 for i, m in enumerate(masks) for k in masks[i + 1:])
 
 
+def test_split_transforms_start_at_six_ranks_and_can_be_switched_off(monkeypatch):
+    """from six ranks on a sharded proof splits every coset transform in halves over two ranks (rank 2 * poly + parity);
+    G16_SPLIT_TRANSFORMS=0 keeps whole transforms on ranks 0-2"""
+    pkg = load_pkg()
+    monkeypatch.delenv("G16_SPLIT_TRANSFORMS", raising=False)
+    assert [pkg.split_transforms(w) for w in (1, 2, 3, 4, 5, 6, 7, 8, 16)] == [False] * 5 + [True] * 4
+    owners = sorted((r // 2, r % 2) for r in range(6))
+    assert owners == [(p, t) for p in range(3) for t in range(2)]        # every (polynomial, parity) has exactly one owner
+    monkeypatch.setenv("G16_SPLIT_TRANSFORMS", "0")
+    assert not pkg.split_transforms(8)
+
+
 WORKER = r'''
 import os, sys
 sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
