@@ -4,13 +4,15 @@ CSRC     := $(PKG)/csrc
 NVCC     ?= nvcc
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
-OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o $(CSRC)/poseidon.o $(CSRC)/verify.o $(CSRC)/merkle.o $(CSRC)/setup.o $(CSRC)/zkey_new.o
-HDRS     := $(wildcard $(CSRC)/*.cuh) $(filter-out $(CSRC)/service% $(CSRC)/verify%,$(wildcard $(CSRC)/*.hpp)) include/g16_b200.h
+OBJS     := $(CSRC)/prover.o $(CSRC)/ops.o $(CSRC)/msm.o $(CSRC)/poseidon.o $(CSRC)/verify.o $(CSRC)/merkle.o $(CSRC)/setup.o $(CSRC)/zkey_new.o $(CSRC)/wtns_check.o
+HDRS     := $(wildcard $(CSRC)/*.cuh) $(filter-out $(CSRC)/service% $(CSRC)/verify% $(CSRC)/binfile_ro%,$(wildcard $(CSRC)/*.hpp)) include/g16_b200.h
 
 all: $(PKG)/libg16b200.so $(PKG)/libg16synth.so $(PKG)/prover
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(HDRS)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(CSRC)/zkey_new.o $(CSRC)/wtns_check.o: $(CSRC)/binfile_ro.hpp
 
 $(CSRC)/verify.o: $(CSRC)/verify.cpp $(wildcard $(CSRC)/verify*.hpp) $(CSRC)/hostfield.hpp include/g16_b200.h
 	g++ -O2 -std=c++17 -fPIC -Wall -Iinclude -c $< -o $@

@@ -252,6 +252,12 @@ int g16_merkle_root_static(const void* d_rows, size_t n_rows, void* d_root, void
  * ceremony", G16_ERR_FORMAT for malformed files or a ceremony file that is not prepared. */
 int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const char* zkey_out, const g16_opts* opts,
                  uint8_t cs_hash_out[64]);
+/* `snarkjs wtns check <circuit.r1cs> <witness.wtns>` (scripts/g16_verify.sh:205-209, behind the reference's -w flag):
+ * <A_c, w> * <B_c, w> == <C_c, w> for every constraint, one GPU thread per constraint.  Returns G16_OK when the check RAN;
+ * *first_bad_constraint is -1 for a satisfying witness, else the lowest index of a constraint that fails.  Errors:
+ * G16_ERR_CURVE (another field), G16_ERR_WITNESS_LEN ("Invalid witness length. Circuit: N, witness: M"), G16_ERR_FORMAT
+ * (malformed files, values not below r, wire 0 not the constant 1). */
+int g16_wtns_check(const char* r1cs_path, const char* wtns_path, const g16_opts* opts, int64_t* first_bad_constraint);
 int g16_zkey_contribute(const char* zkey_in, const char* zkey_out, const char* name, const uint8_t* entropy, size_t entropy_len,
                         const g16_opts* opts, uint8_t contribution_hash[64]);
 /* delta' from 2^num_iterations_exp iterations of SHA-256 over beacon_hash (scripts/g16_setup.sh:272-277) */

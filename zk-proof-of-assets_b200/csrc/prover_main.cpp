@@ -15,6 +15,8 @@
 //                                   the limb file scripts/sanitize_groth16_proof.py:112-123 writes, byte for byte
 // Anonymity-set Merkle tree (the argv of the reference's `merkle-tree`, scripts/merkle_tree.rs:29-44):
 //     prover --merkle-tree --anon-set <csv> --poa-input-data <json> --output-dir <dir>
+// Witness check (the argv of `snarkjs wtns check`, scripts/g16_verify.sh:205-209):
+//     prover --wtns-check <circuit.r1cs> <witness.wtns>       exit 0 + "WITNESS IS CORRECT" | exit 1 + "WITNESS CHECKING FAILED"
 // Setup steps (snarkjs' argument order, scripts/g16_setup.sh:239-295):
 //     prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>
 //     prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
@@ -212,6 +214,25 @@ static int setup_cli(int argc, char** argv) {
     return 0;
 }
 
+static int wtns_check_cli(int argc, char** argv) {
+    if (argc != 4) {
+        std::fprintf(stderr, "Usage: prover --wtns-check <circuit.r1cs> <witness.wtns>\n");
+        return 2;
+    }
+    int64_t bad = -1;
+    int rc = g16_wtns_check(argv[2], argv[3], nullptr, &bad);
+    if (rc != G16_OK) {
+        std::fprintf(stderr, "%s\n", g16_last_error());
+        return rc;
+    }
+    if (bad >= 0) {
+        std::printf("WITNESS CHECKING FAILED: constraint %lld is not satisfied\n", (long long)bad);
+        return 1;
+    }
+    std::printf("WITNESS IS CORRECT\n");
+    return 0;
+}
+
 int main(int argc, char** argv) {
     // every mode but --serve does ONE job in this process: the library's 32 hardware queues would save 0.7 ms of a proof
     // and cost 0.6 s of CUDA context creation.  Keep CUDA's default unless the user chose a value (the variable is read
@@ -220,6 +241,7 @@ int main(int argc, char** argv) {
         ::setenv("CUDA_DEVICE_MAX_CONNECTIONS", "8", 1);
     if (argc >= 2 && !std::strcmp(argv[1], "--merkle-tree")) return merkle_cli(argc, argv);
     if (argc >= 2 && !std::strncmp(argv[1], "--zkey-", 7)) return setup_cli(argc, argv);
+    if (argc >= 2 && !std::strcmp(argv[1], "--wtns-check")) return wtns_check_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--verify") || !std::strcmp(argv[1], "--sanitize"))) return verify_cli(argc, argv);
     if (argc >= 2 && (!std::strcmp(argv[1], "--serve") || !std::strcmp(argv[1], "--ping") ||
                       !std::strcmp(argv[1], "--stats") || !std::strcmp(argv[1], "--shutdown")))
