@@ -252,6 +252,15 @@ int g16_merkle_root_static(const void* d_rows, size_t n_rows, void* d_root, void
  * ceremony", G16_ERR_FORMAT for malformed files or a ceremony file that is not prepared. */
 int g16_zkey_new(const char* r1cs_path, const char* ptau_path, const char* zkey_out, const g16_opts* opts,
                  uint8_t cs_hash_out[64]);
+/* `snarkjs zkey verify <circuit.r1cs> <pot_final.ptau> <circuit_final.zkey>` (scripts/g16_verify.sh:190-202, behind the
+ * reference's -z flag): g16_zkey_new makes the initial key again (GPU, temporary file under $TMPDIR), then the key under test
+ * must equal it in the header's alpha/beta/gamma, the circuit hash and sections 3-7; every contribution record must carry
+ * the right transcript, a valid proof of knowledge and a delta that follows from the previous one (pairing checks on the
+ * host), a beacon record must be the beacon it names; and sections 8 and 9 must be the initial sections divided by delta
+ * (random linear combinations, four MSMs on the GPU, two pairing checks).  G16_OK = valid; G16_ERR_GENERIC with the first
+ * failed check in g16_last_error otherwise.  Transcript and proof-of-knowledge conventions are this library's own
+ * (g16_zkey_contribute): a key contributed to by snarkjs itself is NOT expected to pass, nor the reverse. */
+int g16_zkey_verify(const char* r1cs_path, const char* ptau_path, const char* zkey_path, const g16_opts* opts);
 /* `snarkjs wtns check <circuit.r1cs> <witness.wtns>` (scripts/g16_verify.sh:205-209, behind the reference's -w flag):
  * <A_c, w> * <B_c, w> == <C_c, w> for every constraint, one GPU thread per constraint.  Returns G16_OK when the check RAN;
  * *first_bad_constraint is -1 for a satisfying witness, else the lowest index of a constraint that fails.  Errors:

@@ -235,3 +235,90 @@ def export_vkey(zkey_bytes):
           "vk_gamma_2": g2j(gamma2), "vk_delta_2": g2j(delta2), "vk_alphabeta_12": tower,
           "IC": [g1j(_g1_from_lem(secs[3][64 * i:64 * i + 64])) for i in range(npub + 1)]}
     return json.dumps(vk, indent=1)
+
+
+# ---- zkey verify (scripts/g16_verify.sh:190-202: `snarkjs zkey verify <r1cs> <ptau> <zkey>`) ------------------------------
+def same_ratio(a1, a2, b1, b2):
+    """e(a1, b2) == e(a2, b1): (a1, a2) in G1 and (b1, b2) in G2 differ by the same factor"""
+    return bn.pairing(b2, a1) == bn.pairing(b1, a2)
+
+
+def parse_params(params):
+    """-> (name | None, (beacon hash, exp) | None) of a contribution's parameter bytes"""
+    name, exp, bh, pos = None, None, None, 0
+    while pos < len(params):
+        t = params[pos]
+        if t == 1:
+            n = params[pos + 1]
+            name = params[pos + 2:pos + 2 + n].decode()
+            pos += 2 + n
+        elif t == 2:
+            exp = params[pos + 1]
+            pos += 2
+        elif t == 3:
+            n = params[pos + 1]
+            bh = bytes(params[pos + 2:pos + 2 + n])
+            pos += 2 + n
+        else:
+            raise ValueError("zkey: unknown contribution parameter %d" % t)
+    return name, ((bh, exp) if bh is not None and exp is not None else None)
+
+
+def verify_from_init(init_zkey, zkey, rng):
+    """snarkjs zkey_verify_frominit.js on THIS repository's transcript conventions: `init_zkey` is what `zkey new` makes from the
+    circuit and the ceremony file (oracle/zkey_new.py), `zkey` the key under test.  -> None when the key is the initial key
+    plus a valid chain of contributions, else a string naming the first check that fails.  rng: random.Random for the
+    coefficients of the random linear combinations over sections 8 and 9."""
+    si, sz = parse_sections(init_zkey), parse_sections(zkey)
+    o = 4 + 32 + 4 + 32 + 12
+    if sz[1] != si[1]:
+        return "not a groth16 key"
+    if sz[2][:o + 384] != si[2][:o + 384]:
+        return "header differs from the initial key (sizes, alpha, beta or gamma)"
+    for t, what in ((3, "IC"), (4, "coefficients"), (5, "A"), (6, "B1"), (7, "B2")):
+        if sz[t] != si[t]:
+            return "section %d (%s) differs from the initial key" % (t, what)
+    cs_i, _ = parse_mpc(si[10])
+    cs, contribs = parse_mpc(sz[10])
+    if cs != cs_i:
+        return "circuit hash differs from the initial key"
+    cur = _g1_from_lem(si[2][o + 384:o + 448])
+    seen = []
+    for i, c in enumerate(contribs):
+        pts = c["points"]
+        after, g1_s, g1_sx = (_g1_from_lem(pts[64 * k:64 * k + 64]) for k in range(3))
+        g2_spx = _g2_from_lem(pts[192:320])
+        if None in (after, g1_s, g1_sx, g2_spx):
+            return "contribution %d: point at infinity" % (i + 1)
+        transcript = blake(cs, *[hash_pubkey(p) for p in seen], hash_g1(g1_s), hash_g1(g1_sx))
+        if transcript != c["transcript"]:
+            return "contribution %d: transcript mismatch" % (i + 1)
+        g2_sp = hash_to_g2(transcript)
+        if not same_ratio(g1_s, g1_sx, g2_sp, g2_spx):
+            return "contribution %d: invalid proof of knowledge" % (i + 1)
+        if not same_ratio(cur, after, g2_sp, g2_spx):
+            return "contribution %d: delta does not follow from the previous one" % (i + 1)
+        _, beacon = parse_params(c["params"])
+        if beacon is not None:
+            d, s = derive(beacon_seed(*beacon))
+            want_s = bn.G1.mul(bn.G1_GEN, s)
+            if g1_s != want_s or g1_sx != bn.G1.mul(want_s, d):
+                return "contribution %d: not the beacon it claims to be" % (i + 1)
+        cur = after
+        seen.append(c)
+    delta1 = _g1_from_lem(sz[2][o + 384:o + 448])
+    delta2 = _g2_from_lem(sz[2][o + 448:o + 576])
+    if delta1 != cur:
+        return "delta in the header is not the last contribution's"
+    if not same_ratio(bn.G1_GEN, delta1, bn.G2_GEN, delta2):
+        return "delta1 and delta2 differ"
+    for t, what in ((8, "C"), (9, "H")):
+        if len(sz[t]) != len(si[t]):
+            return "section %d (%s) has the wrong size" % (t, what)
+        n = len(sz[t]) // 64
+        r = [rng.getrandbits(128) | 1 for _ in range(n)]
+        a1 = bn.G1.msm([_g1_from_lem(si[t][64 * k:64 * k + 64]) for k in range(n)], r)
+        a2 = bn.G1.msm([_g1_from_lem(sz[t][64 * k:64 * k + 64]) for k in range(n)], r)
+        if (a1 is None) != (a2 is None) or (a1 is not None and not same_ratio(a1, a2, delta2, bn.G2_GEN)):
+            return "section %d (%s) is not the initial section divided by delta" % (t, what)
+    return None

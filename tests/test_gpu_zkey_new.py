@@ -137,8 +137,73 @@ def test_zkey_new_at_scale_agrees_with_the_fixture_generator_and_proves(pkg, tmp
     with pkg.ZKey(got) as zk:
         proof, public = zk.prove(wtns)
     assert pkg.verify(vkey, public, proof)
+    # the rest of the reference's setup on the new key: contribute, then `zkey verify` of the result against circuit + ceremony
+    del got, ref
+    pkg.zkey_contribute(tmp_path / "new.zkey", tmp_path / "c1.zkey", name="first", entropy="e")
+    t0 = time.perf_counter()
+    assert pkg.zkey_verify(tmp_path / "c.r1cs", tmp_path / "pot.ptau", tmp_path / "c1.zkey")
+    dv = time.perf_counter() - t0
     out = os.path.join(ROOT, "gpurun_out")
     if os.path.isdir(out):
         with open(os.path.join(out, "zkey_new_%d.json" % n_cons), "w") as f:
             json.dump({"n_vars": n_vars, "n_public": n_public, "n_constraints": n_cons, "zkey_new_wall_s": dt,
-                       "zkey_bytes": len(got)}, f)
+                       "zkey_verify_wall_s": dv, "zkey_bytes": os.path.getsize(tmp_path / "new.zkey")}, f)
+
+
+def test_zkey_verify_agrees_with_the_oracle(pkg, small, tmp_path):
+    """`zkey verify` (scripts/g16_verify.sh:190-202): the fresh key, a chain of this library's contributions and a chain made
+    by the oracle all pass, in the library and in the oracle; broken keys are refused with the check that failed"""
+    import random
+    from oracle import setup as S
+    d = small["dir"]
+    r1cs, ptau = d / "c.r1cs", d / "pot8.ptau"
+    pkg.zkey_new(r1cs, ptau, tmp_path / "k0.zkey")
+    assert pkg.zkey_verify(r1cs, ptau, tmp_path / "k0.zkey")
+    pkg.zkey_contribute(tmp_path / "k0.zkey", tmp_path / "k1.zkey", name="first", entropy="abc")
+    pkg.zkey_beacon(tmp_path / "k1.zkey", tmp_path / "k2.zkey", "0102030405060708090a0b0c0d0e0f101112131415161718191a1b1c1d1e1f", 4, name="final")
+    assert pkg.zkey_verify(r1cs, ptau, tmp_path / "k2.zkey")
+    init = (tmp_path / "k0.zkey").read_bytes()
+    k2 = (tmp_path / "k2.zkey").read_bytes()
+    assert S.verify_from_init(init, k2, random.Random(1)) is None            # the oracle accepts the library's chain
+    ok, _ = S.contribute(init, "oracle", b"oracle entropy")
+    (tmp_path / "o1.zkey").write_bytes(ok)
+    assert pkg.zkey_verify(r1cs, ptau, tmp_path / "o1.zkey")                  # and the library the oracle's
+    secs = sections(k2)
+
+    def rebuilt(changes, name):
+        out = bytearray(b"zkey" + (1).to_bytes(4, "little") + (10).to_bytes(4, "little"))
+        for t in range(1, 11):
+            body = changes.get(t, secs[t])
+            out += t.to_bytes(4, "little") + len(body).to_bytes(8, "little") + body
+        (tmp_path / name).write_bytes(bytes(out))
+        return tmp_path / name
+    s8 = bytearray(secs[8])
+    s8[0:64], s8[64:128] = s8[64:128], s8[0:64]
+    with pytest.raises(pkg.G16Error, match=r"section 8 \(C\) is not the initial section divided by delta"):
+        pkg.zkey_verify(r1cs, ptau, rebuilt({8: bytes(s8)}, "b8.zkey"))
+    s9 = bytearray(secs[9])
+    s9[64:128] = s9[0:64]
+    with pytest.raises(pkg.G16Error, match=r"section 9 \(H\)"):
+        pkg.zkey_verify(r1cs, ptau, rebuilt({9: bytes(s9)}, "b9.zkey"))
+    s5 = bytearray(secs[5])
+    s5[0:64] = s5[64:128]
+    with pytest.raises(pkg.G16Error, match=r"section 5 \(A\) differs"):
+        pkg.zkey_verify(r1cs, ptau, rebuilt({5: bytes(s5)}, "b5.zkey"))
+    s10 = bytearray(secs[10])
+    s10[-1] ^= 1
+    with pytest.raises(pkg.G16Error, match="not the beacon it claims to be"):
+        pkg.zkey_verify(r1cs, ptau, rebuilt({10: bytes(s10)}, "b10.zkey"))
+    s10 = bytearray(secs[10])
+    s10[68 + 64 + 5] ^= 1                              # first record's g1_s: no longer what the transcript hashed
+    with pytest.raises(pkg.G16Error, match="contribution 1"):
+        pkg.zkey_verify(r1cs, ptau, rebuilt({10: bytes(s10)}, "b10b.zkey"))
+    other = tmp_path / "other.zkey"
+    pkg.zkey_contribute(tmp_path / "k0.zkey", other, name="first", entropy="another")
+    so = sections(other.read_bytes())
+    with pytest.raises(pkg.G16Error, match="delta"):
+        pkg.zkey_verify(r1cs, ptau, rebuilt({10: sections((tmp_path / "k1.zkey").read_bytes())[10], 2: so[2], 8: so[8], 9: so[9]}, "bd.zkey"))
+    exe = os.path.join(ROOT, "zk-proof-of-assets_b200", "prover")
+    r = subprocess.run([exe, "--zkey-verify", str(r1cs), str(ptau), str(tmp_path / "k2.zkey")], capture_output=True, text=True)
+    assert r.returncode == 0 and "ZKey Ok!" in r.stdout, r.stderr
+    r = subprocess.run([exe, "--zkey-verify", str(r1cs), str(ptau), str(tmp_path / "b8.zkey")], capture_output=True, text=True)
+    assert r.returncode == 1 and "section 8" in r.stderr

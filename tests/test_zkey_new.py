@@ -61,3 +61,41 @@ def test_zkey_new_with_a_ceremony_of_the_circuits_own_power_proves_and_verifies(
     assert V.verify(case["vkey"], json.loads(public), json.loads(proof))
     with pytest.raises(ValueError, match="circuit too big"):
         ZN.zkey_new(case["r1cs"], ZN.write_ptau(td.tau, td.alpha, td.beta, 6))
+
+
+def test_zkey_verify_oracle_accepts_a_chain_of_contributions_and_names_what_is_broken(case):
+    """`zkey verify` (scripts/g16_verify.sh:190-202) = the initial key recomputed from circuit + ceremony, then the chain of
+    contributions and the two delta-scaled sections checked against it"""
+    import random
+    td = case["td"]
+    init = ZN.zkey_new(case["r1cs"], ZN.write_ptau(td.tau, td.alpha, td.beta, 8))
+    rng = random.Random(5)
+    assert S.verify_from_init(init, init, rng) is None
+    k1, _ = S.contribute(init, "first", b"entropy one")
+    bh = bytes(range(1, 33))
+    k2, _ = S.contribute(k1, "beacon", S.beacon_seed(bh, 3), beacon=(bh, 3))
+    assert S.verify_from_init(init, k1, rng) is None
+    assert S.verify_from_init(init, k2, rng) is None
+    secs = sections(k2)
+
+    def rebuilt(changes):
+        out = bytearray(b"zkey" + (1).to_bytes(4, "little") + (10).to_bytes(4, "little"))
+        for t in range(1, 11):
+            body = changes.get(t, secs[t])
+            out += t.to_bytes(4, "little") + len(body).to_bytes(8, "little") + body
+        return bytes(out)
+    # a point of section 8 swapped for another valid point
+    s8 = bytearray(secs[8])
+    s8[0:64], s8[64:128] = s8[64:128], s8[0:64]
+    assert "section 8" in S.verify_from_init(init, rebuilt({8: bytes(s8)}), rng)
+    s5 = bytearray(secs[5])
+    s5[0:64] = s5[64:128]
+    assert "section 5" in S.verify_from_init(init, rebuilt({5: bytes(s5)}), rng)
+    # a contribution whose delta does not follow: splice k1's record into a key whose sections were scaled by another secret
+    other, _ = S.contribute(init, "first", b"another entropy")
+    so = sections(other)
+    assert "delta" in S.verify_from_init(init, rebuilt({10: sections(k1)[10], 2: so[2], 8: so[8], 9: so[9]}), rng)
+    # the beacon record claims another beacon hash
+    s10 = bytearray(secs[10])
+    s10[-1] ^= 1
+    assert "beacon" in S.verify_from_init(init, rebuilt({10: bytes(s10)}), rng)

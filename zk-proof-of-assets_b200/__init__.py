@@ -44,7 +44,7 @@ ABI_SYMBOLS = [
     "g16_prove_partial_joined", "g16_prove_begin", "g16_h_transform_half", "g16_prove_partial_joined_halves", "g16_verify", "g16_sanitize",
     "g16_poseidon_hash2", "g16_merkle_build", "g16_merkle_close", "g16_merkle_info", "g16_merkle_root", "g16_merkle_node",
     "g16_merkle_proof", "g16_merkle_find", "g16_merkle_files", "g16_merkle_root_static",
-    "g16_zkey_new", "g16_wtns_check", "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash", "g16_test_msm_shape",
+    "g16_zkey_new", "g16_zkey_verify", "g16_wtns_check", "g16_zkey_contribute", "g16_zkey_beacon", "g16_zkey_export_vkey", "g16_test_hash", "g16_test_msm_shape",
 ]
 SYNTH_SYMBOLS = [
     "g16_synth_create", "g16_synth_destroy", "g16_synth_sizes", "g16_synth_write", "g16_synth_expected",
@@ -142,6 +142,7 @@ def lib():
         L.g16_merkle_files.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
         L.g16_merkle_root_static.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_zkey_new.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_void_p]
+        L.g16_zkey_verify.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p]
         L.g16_wtns_check.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_void_p, ctypes.c_void_p]
         L.g16_zkey_contribute.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_size_t,
                                           ctypes.c_void_p, ctypes.c_void_p]
@@ -613,6 +614,14 @@ def zkey_new(r1cs_path, ptau_path, zkey_out, device=-1):
     h = ctypes.create_string_buffer(64)
     _check(lib().g16_zkey_new(os.fsencode(r1cs_path), os.fsencode(ptau_path), os.fsencode(zkey_out), ctypes.byref(o), h))
     return h.raw
+
+
+def zkey_verify(r1cs_path, ptau_path, zkey_path, device=-1):
+    """`snarkjs zkey verify <circuit.r1cs> <pot.ptau> <zkey>` (scripts/g16_verify.sh:190-202): raises G16Error naming the first
+    failed check; returns True for a key that is `zkey new` of the circuit plus a valid chain of this library's contributions"""
+    o = make_opts(device=device)
+    _check(lib().g16_zkey_verify(os.fsencode(r1cs_path), os.fsencode(ptau_path), os.fsencode(zkey_path), ctypes.byref(o)))
+    return True
 
 
 def wtns_check(r1cs_path, wtns_path, device=-1):

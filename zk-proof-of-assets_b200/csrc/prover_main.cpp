@@ -22,6 +22,7 @@
 //     prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]
 //     prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]
 //     prover --zkey-export-vkey <zkey> <verification_key.json>
+//     prover --zkey-verify <circuit.r1cs> <pot_final.ptau> <circuit_final.zkey>      exit 0 + "ZKey Ok!" | exit 1 + the failed check
 #include <unistd.h>
 
 #include <climits>
@@ -175,6 +176,9 @@ static int setup_cli(int argc, char** argv) {
     if (cmd == "--zkey-new" && pos.size() == 3) {
         rc = g16_zkey_new(pos[0].c_str(), pos[1].c_str(), pos[2].c_str(), nullptr, h);
         if (rc == G16_OK) std::printf("Circuit Hash: \n\t\t%s\n", hex(h).c_str());
+    } else if (cmd == "--zkey-verify" && pos.size() == 3) {
+        rc = g16_zkey_verify(pos[0].c_str(), pos[1].c_str(), pos[2].c_str(), nullptr);
+        if (rc == G16_OK) std::printf("ZKey Ok!\n");
     } else if (cmd == "--zkey-contribute" && pos.size() == 2) {
         rc = g16_zkey_contribute(pos[0].c_str(), pos[1].c_str(), name.c_str(), has_entropy ? (const uint8_t*)entropy.data() : nullptr,
                                  entropy.size(), nullptr, h);
@@ -204,7 +208,8 @@ static int setup_cli(int argc, char** argv) {
         std::fprintf(stderr, "Usage: prover --zkey-new <circuit.r1cs> <pot_final.ptau> <circuit_0000.zkey>\n"
                              "       prover --zkey-contribute <in.zkey> <out.zkey> [--name=NAME] [-e=ENTROPY]\n"
                              "       prover --zkey-beacon <in.zkey> <out.zkey> <beaconHash hex> <numIterationsExp> [-n=NAME]\n"
-                             "       prover --zkey-export-vkey <zkey> <verification_key.json>\n");
+                             "       prover --zkey-export-vkey <zkey> <verification_key.json>\n"
+                             "       prover --zkey-verify <circuit.r1cs> <pot_final.ptau> <circuit_final.zkey>\n");
         return 2;
     }
     if (rc != G16_OK) {

@@ -354,6 +354,121 @@ int contribute(const char* in_path, const char* out_path, const char* name, cons
 
 std::string dec(const U256& mont) { return "\"" + u256_to_dec(HFq::from_mont(mont)) + "\""; }
 
+// ---- zkey verify -----------------------------------------------------------------------------------------------------
+// e(a1, b2) == e(a2, b1): (a1, a2) in G1 and (b1, b2) in G2 differ by the same factor.  One two-pair Miller loop.
+bool same_ratio(const HAffine<HFq>& a1, const HAffine<HFq>& a2, const HAffine<HFq2>& b1, const HAffine<HFq2>& b2) {
+    HAffine<HFq> na2 = a2;
+    if (!na2.inf) na2.y = HFq::neg(na2.y);
+    g16v::f12 f = g16v::miller_loop_multi({g16v::PairingInput{b2, a1}, g16v::PairingInput{b1, na2}});
+    return g16v::f12_eq(g16v::final_exponentiate(f), g16v::f12_one());
+}
+
+bool g1_eq(const HAffine<HFq>& a, const HAffine<HFq>& b) {
+    if (a.inf || b.inf) return a.inf == b.inf;
+    return u256_eq(a.x, b.x) && u256_eq(a.y, b.y);
+}
+
+// the checks of snarkjs zkey_verify_frominit.js on this library's transcript conventions; "" = valid, else what failed
+std::string verify_from_init(const bytes& init, const bytes& z, const g16_opts* opts) {
+    Sec si[11], sz[11];
+    parse_zkey(init, si);
+    parse_zkey(z, sz);
+    const size_t o = 4 + 32 + 4 + 32 + 12;
+    auto same = [](const Sec& a, const Sec& b) { return a.size == b.size && std::memcmp(a.p, b.p, a.size) == 0; };
+    if (!same(sz[1], si[1])) return "not a groth16 key";
+    if (sz[2].size != si[2].size || std::memcmp(sz[2].p, si[2].p, o + 384) != 0)
+        return "header differs from the initial key (sizes, alpha, beta or gamma)";
+    const char* names[8] = {"", "", "", "IC", "coefficients", "A", "B1", "B2"};
+    for (int t = 3; t <= 7; t++)
+        if (!same(sz[t], si[t])) return "section " + std::to_string(t) + " (" + names[t] + ") differs from the initial key";
+    if (std::memcmp(sz[10].p, si[10].p, 64) != 0) return "circuit hash differs from the initial key";
+    HAffine<HFq> cur = g1_rec(si[2].p + o + 384);
+    const HAffine<HFq> gen1{HFq::one(), HFq::add(HFq::one(), HFq::one()), false};
+    const uint8_t* mp = sz[10].p;
+    uint32_t ncontrib;
+    std::memcpy(&ncontrib, mp + 64, 4);
+    Blake2b th(64);
+    th.update(mp, 64);
+    size_t pos = 68;
+    for (uint32_t i = 0; i < ncontrib; i++) {
+        const std::string who = "contribution " + std::to_string(i + 1) + ": ";
+        if (pos + 388 > sz[10].size) return "contributions section is truncated";
+        const uint8_t* rec = mp + pos;
+        uint32_t plen;
+        std::memcpy(&plen, rec + 384, 4);
+        if (plen > sz[10].size - pos - 388) return "contributions section is truncated";
+        HAffine<HFq> after = g1_rec(rec), g1_s = g1_rec(rec + 64), g1_sx = g1_rec(rec + 128);
+        HAffine<HFq2> g2_spx = g2_rec(rec + 192);
+        if (after.inf || g1_s.inf || g1_sx.inf || g2_spx.inf) return who + "point at infinity";
+        Blake2b t2 = th;
+        hash_g1(t2, g1_s);
+        hash_g1(t2, g1_sx);
+        bytes transcript = t2.digest();
+        if (std::memcmp(transcript.data(), rec + 320, 64) != 0) return who + "transcript mismatch";
+        HAffine<HFq2> g2_sp = hash_to_g2(transcript);
+        if (!same_ratio(g1_s, g1_sx, g2_sp, g2_spx)) return who + "invalid proof of knowledge";
+        if (!same_ratio(cur, after, g2_sp, g2_spx)) return who + "delta does not follow from the previous one";
+        // parameters: 1 len name | 2 exp | 3 len beaconHash
+        const uint8_t* pp = rec + 388;
+        const uint8_t* bh = nullptr;
+        size_t bh_len = 0;
+        int exp = -1;
+        for (size_t k = 0; k < plen;) {
+            uint8_t t = pp[k];
+            if (t == 1 && k + 1 < plen && k + 2 + pp[k + 1] <= plen) k += 2 + pp[k + 1];
+            else if (t == 2 && k + 1 < plen) { exp = pp[k + 1]; k += 2; }
+            else if (t == 3 && k + 1 < plen && k + 2 + pp[k + 1] <= plen) { bh = pp + k + 2; bh_len = pp[k + 1]; k += 2 + bh_len; }
+            else return who + "malformed parameters";
+        }
+        if (bh && exp >= 0) {
+            if (exp > 63) return who + "beacon exponent above 63";
+            bytes seed(bh, bh + bh_len);
+            for (uint64_t it = 0; it < (uint64_t(1) << exp); it++) seed = sha256(seed.data(), seed.size());
+            U256 d = le_mod(blake({tagged("delta"), seed}), HFr::mod(), false);
+            U256 sc = le_mod(blake({tagged("s"), seed}), HFr::mod(), false);
+            if (u256_is_zero(d)) d = U256{{1, 0, 0, 0}};
+            if (u256_is_zero(sc)) sc = U256{{1, 0, 0, 0}};
+            HAffine<HFq> want_s = HG1::to_affine(HG1::mul(HG1::from_affine(gen1), sc));
+            HAffine<HFq> want_sx = HG1::to_affine(HG1::mul(HG1::from_affine(want_s), d));
+            if (!g1_eq(g1_s, want_s) || !g1_eq(g1_sx, want_sx)) return who + "not the beacon it claims to be";
+        }
+        cur = after;
+        hash_pubkey(th, rec);
+        pos += 388 + plen;
+    }
+    if (pos != sz[10].size) return "contributions section has trailing bytes";
+    HAffine<HFq> delta1 = g1_rec(sz[2].p + o + 384);
+    HAffine<HFq2> delta2 = g2_rec(sz[2].p + o + 448);
+    if (!g1_eq(delta1, cur)) return "delta in the header is not the last contribution's";
+    HAffine<HFq2> gen2 = g2_rec(si[2].p + o + 448);   // the initial key's delta2 is the generator
+    if (!same_ratio(gen1, delta1, gen2, delta2)) return "delta1 and delta2 differ";
+    // sections 8 (C) and 9 (H): a random linear combination of the initial section and the same combination of the key's
+    // differ by delta (two MSMs on the GPU per section, 128-bit coefficients from the kernel's CSPRNG)
+    for (int t = 8; t <= 9; t++) {
+        const std::string what = "section " + std::to_string(t) + (t == 8 ? " (C)" : " (H)");
+        if (sz[t].size != si[t].size) return what + " has the wrong size";
+        size_t n = sz[t].size / 64;
+        if (!n) continue;
+        bytes r(n * 32, 0);
+        for (size_t k = 0; k < n; k++) {
+            size_t got = 0;
+            while (got < 16) {
+                ssize_t w = getrandom(&r[k * 32 + got], 16 - got, 0);
+                if (w < 0 && errno != EINTR) throw std::runtime_error("getrandom failed");
+                if (w > 0) got += size_t(w);
+            }
+            r[k * 32] |= 1;
+        }
+        uint8_t a1[64], a2[64];
+        int rc = g16_msm_g1_host(si[t].p, r.data(), n, a1, opts);
+        if (rc == G16_OK) rc = g16_msm_g1_host(sz[t].p, r.data(), n, a2, opts);
+        if (rc != G16_OK) throw std::runtime_error(g16_last_error());
+        HAffine<HFq> p1 = g1_rec(a1), p2 = g1_rec(a2);
+        if (p1.inf != p2.inf || (!p1.inf && !same_ratio(p1, p2, delta2, gen2))) return what + " is not the initial section divided by delta";
+    }
+    return "";
+}
+
 }  // namespace
 
 extern "C" {
@@ -389,6 +504,28 @@ int g16_zkey_beacon(const char* zkey_in, const char* zkey_out, const char* name,
         return contribute(zkey_in, zkey_out, name, cur, beacon_hash, hash_len, num_iterations_exp, opts, contribution_hash);
     } catch (const std::exception& e) {
         return g16::fail(G16_ERR_FORMAT, std::string("zkey beacon: ") + e.what());
+    }
+}
+
+// `snarkjs zkey verify <circuit.r1cs> <pot.ptau> <circuit_final.zkey>` (scripts/g16_verify.sh:190-202): the initial key is made
+// again from the circuit and the ceremony file (g16_zkey_new, on the GPU, into a temporary file), then the key under test must
+// be that key plus a valid chain of contributions.
+int g16_zkey_verify(const char* r1cs_path, const char* ptau_path, const char* zkey_path, const g16_opts* opts) {
+    if (!r1cs_path || !ptau_path || !zkey_path) return g16::fail(G16_ERR_GENERIC, "null argument");
+    const char* td = std::getenv("TMPDIR");
+    std::string tmp = std::string(td && *td ? td : "/tmp") + "/g16_zkey_verify." + std::to_string((long)getpid()) + ".zkey";
+    try {
+        int rc = g16_zkey_new(r1cs_path, ptau_path, tmp.c_str(), opts, nullptr);
+        if (rc != G16_OK) return rc;
+        bytes init = read_all(tmp.c_str());
+        std::remove(tmp.c_str());
+        bytes z = read_all(zkey_path);
+        std::string why = verify_from_init(init, z, opts);
+        if (!why.empty()) return g16::fail(G16_ERR_GENERIC, "zkey verify: " + why);
+        return G16_OK;
+    } catch (const std::exception& e) {
+        std::remove(tmp.c_str());
+        return g16::fail(G16_ERR_FORMAT, std::string("zkey verify: ") + e.what());
     }
 }
 
