@@ -118,3 +118,11 @@ def test_msm_index_limits_are_enforced_before_any_sort():
     with pytest.raises(pkg.G16Error) as e:
         pkg.msm_shape(1 << 31, c=24)
     assert "31-bit base indices" in e.value.message
+
+
+def test_headers_are_plain_c():
+    """the boundary is a C ABI: both headers must compile as C99 on their own (what a cgo / N-API / ctypes binding includes)"""
+    for h in ("g16_b200.h", "g16_synth.h"):
+        r = subprocess.run(["gcc", "-x", "c", "-std=c99", "-Wall", "-Werror", "-fsyntax-only", os.path.join(ROOT, "include", h)],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
